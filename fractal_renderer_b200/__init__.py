@@ -1,0 +1,181 @@
+"""fractal_renderer_b200 — B200-native drop-in for the escape-time path of Icelk/fractal-renderer.
+
+Host-side mirror of the reference's public interface for this path (same names and argument meaning):
+
+    reference (Rust)                                   here
+    -------------------------------------------------  ---------------------------------------------
+    calc::Config / Imaginary / RGB / Algo              Config / Imaginary / RGB / Algo   (calc.py)
+    get_image(&Config) -> Vec<RGB>  (src/lib.rs:253)   get_image(config) -> (H*W, 3) uint8 array
+    GUI's RGBA expansion            (src/gui.rs:62-75) get_image_rgba(config) -> (H, W, 4) uint8 array
+    calc::recursive per pixel       (calc/src/lib.rs:245) render_counts(config) -> (iters, zfinal)
+
+All pixels are computed by the CUDA library behind include/frb.h (libfrb.so); nothing here computes a pixel on the
+CPU, and nothing here imports oracle/.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import (FRB_RGB24, FRB_RGBA32, KERNEL_AUTO, KERNEL_NAMES, KERNEL_SIMPLE, KERNEL_STREAM6, KERNEL_STREAM7,
+                   FrbError, FrbFp64Peak, FrbShard, FrbStats)
+from .calc import RGB, Algo, Config, FrbConfig, Imaginary
+
+__all__ = [
+    "Algo", "Config", "Imaginary", "RGB", "FrbError", "Shard", "get_image", "get_image_rgba", "get_image_into",
+    "render_shard", "render_counts", "render_frames", "render_device_async", "sync_stats", "async_stats", "last_stats",
+    "device_count", "init", "shutdown", "set_kernel_variant", "measure_fp64_peak", "shard_rows", "shard_row_to_y",
+    "FRB_RGB24", "FRB_RGBA32", "KERNEL_AUTO", "KERNEL_STREAM6", "KERNEL_STREAM7", "KERNEL_SIMPLE", "KERNEL_NAMES",
+]
+
+
+class Shard:
+    """One device's share of a frame: interleaved bands of `band_rows` rows (include/frb.h FrbShard)."""
+
+    def __init__(self, index: int = 0, count: int = 1, band_rows: int = 0):
+        self.index, self.count, self.band_rows = index, count, band_rows
+
+    def to_c(self) -> FrbShard:
+        return FrbShard(self.index, self.count, self.band_rows, 0)
+
+    def rows(self, height: int) -> int:
+        return shard_rows(height, self)
+
+    def image_rows(self, height: int) -> np.ndarray:
+        """Image row of every local row of this shard, in output order."""
+        n = self.rows(height)
+        br = self.band_rows if self.band_rows else max(height, 1)
+        lr = np.arange(n, dtype=np.int64)
+        band = lr // br
+        return ((band * self.count + self.index) * br + (lr - band * br)).astype(np.uint32)
+
+
+def _shard_ptr(shard: Optional[Shard]):
+    if shard is None:
+        return None, None
+    s = shard.to_c()
+    return s, ctypes.byref(s)
+
+
+def device_count() -> int:
+    return int(_lib.load().frb_device_count())
+
+
+def init(device_mask: int = 0) -> None:
+    _lib.check(_lib.load().frb_init(device_mask))
+
+
+def shutdown() -> None:
+    _lib.load().frb_shutdown()
+
+
+def set_kernel_variant(variant: int) -> None:
+    _lib.check(_lib.load().frb_set_kernel_variant(variant))
+
+
+def shard_rows(height: int, shard: Optional[Shard]) -> int:
+    _, p = _shard_ptr(shard)
+    return int(_lib.load().frb_shard_rows(height, p))
+
+
+def shard_row_to_y(height: int, shard: Optional[Shard], local_row: int) -> int:
+    _, p = _shard_ptr(shard)
+    return int(_lib.load().frb_shard_row_to_y(height, p, local_row))
+
+
+def last_stats() -> dict:
+    s = FrbStats()
+    _lib.check(_lib.load().frb_last_stats(ctypes.byref(s)))
+    return s.as_dict()
+
+
+def get_image_into(config: Config, out: np.ndarray, fmt: int = FRB_RGB24, device: int = 0) -> np.ndarray:
+    """get_image writing into a caller-owned host buffer (any C-contiguous uint8 array of >= W*H*fmt bytes; a
+    pinned buffer avoids the driver's staging copy).  device = -1 spreads the frame over all GPUs."""
+    if out.dtype != np.uint8 or not out.flags.c_contiguous:
+        raise ValueError("out must be a C-contiguous uint8 array")
+    c = config.to_c()
+    _lib.check(_lib.load().frb_render(ctypes.byref(c), out.ctypes.data, out.nbytes, fmt, device))
+    return out
+
+
+def get_image(config: Config, device: int = 0) -> np.ndarray:
+    """`get_image(&Config) -> Vec<RGB>` (src/lib.rs:253): (H*W, 3) uint8, row-major, fields r,g,b."""
+    out = np.empty((config.height * config.width, 3), np.uint8)
+    return get_image_into(config, out, FRB_RGB24, device)
+
+
+def get_image_rgba(config: Config, device: int = 0) -> np.ndarray:
+    """The RGBA8 frame the reference GUI builds from get_image (src/gui.rs:62-75): (H, W, 4) uint8, alpha 255."""
+    out = np.empty((config.height, config.width, 4), np.uint8)
+    return get_image_into(config, out, FRB_RGBA32, device)
+
+
+def render_shard(config: Config, shard: Shard, fmt: int = FRB_RGB24, device: int = 0,
+                 out: Optional[np.ndarray] = None) -> np.ndarray:
+    """One shard of the frame, compact: (rows, W, fmt) uint8."""
+    rows = shard.rows(config.height)
+    if out is None:
+        out = np.empty((rows, config.width, fmt), np.uint8)
+    c = config.to_c()
+    s, p = _shard_ptr(shard)
+    _lib.check(_lib.load().frb_render_shard(ctypes.byref(c), p, out.ctypes.data, out.nbytes, fmt, device))
+    return out
+
+
+def render_counts(config: Config, shard: Optional[Shard] = None, device: int = 0, want_z: bool = True):
+    """The raw result of calc::recursive for every pixel: (iters (rows, W) uint32, zfinal (rows, W, 2) float64)."""
+    rows = shard_rows(config.height, shard)
+    iters = np.empty((rows, config.width), np.uint32)
+    z = np.empty((rows, config.width, 2), np.float64) if want_z else None
+    c = config.to_c()
+    s, p = _shard_ptr(shard)
+    _lib.check(_lib.load().frb_render_counts(ctypes.byref(c), p, iters.ctypes.data, z.ctypes.data if want_z else None, device))
+    return iters, z
+
+
+def render_frames(configs: Sequence[Config], fmt: int = FRB_RGB24, device: int = -1,
+                  out: Optional[np.ndarray] = None) -> np.ndarray:
+    """Independent frames (zoom animation): frame k on device k % G.  Returns the frames back to back as bytes."""
+    n = len(configs)
+    arr = (FrbConfig * max(n, 1))()
+    total = 0
+    for k, cfg in enumerate(configs):
+        arr[k] = cfg.to_c()
+        total += cfg.width * cfg.height * fmt
+    if out is None:
+        out = np.empty(total, np.uint8)
+    _lib.check(_lib.load().frb_render_frames(arr, n, out.ctypes.data, out.nbytes, fmt, device))
+    return out
+
+
+def render_device_async(config: Config, dev_ptr: int, nbytes: int, fmt: int = FRB_RGB24, device: int = 0,
+                        shard: Optional[Shard] = None, stream: int = 0) -> None:
+    """Enqueue a render into DEVICE memory (`dev_ptr`, 16-byte aligned) on `stream` (cudaStream_t handle, 0 = the
+    library's stream).  No host copies; complete when the stream drains."""
+    c = config.to_c()
+    s, p = _shard_ptr(shard)
+    _lib.check(_lib.load().frb_render_device_async(ctypes.byref(c), p, ctypes.c_void_p(dev_ptr), nbytes, fmt, device,
+                                                   ctypes.c_void_p(stream) if stream else None))
+
+
+def sync_stats() -> dict:
+    s = FrbStats()
+    _lib.check(_lib.load().frb_sync_stats(ctypes.byref(s)))
+    return s.as_dict()
+
+
+def async_stats(back: int = 0) -> dict:
+    """Statistics of the asynchronous render issued `back` calls before the last one by this thread."""
+    s = FrbStats()
+    _lib.check(_lib.load().frb_async_stats(back, ctypes.byref(s)))
+    return s.as_dict()
+
+
+def measure_fp64_peak(device: int = 0) -> dict:
+    p = FrbFp64Peak()
+    _lib.check(_lib.load().frb_measure_fp64_peak(device, ctypes.byref(p)))
+    return {k: getattr(p, k) for k, _ in p._fields_ if k != "reserved"}

@@ -1,0 +1,820 @@
+// frb_api.cu — the C ABI of include/frb.h: device contexts, buffer pools, launches, copies, statistics.
+//
+// Replaces the Mandelbrot|Julia arm of the reference's get_image (src/lib.rs:253-270).  No CPU fallback exists:
+// without a usable CUDA device every compute entry point fails with FRB_ERR_NO_DEVICE.
+#include "../../include/frb.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "frb_kernels.cuh"
+
+namespace {
+
+using frb::RenderParams;
+
+constexpr int kMaxDevices = 32;
+constexpr int kSlots = 64;               // in-flight async renders per device whose statistics stay readable
+constexpr uint32_t kDefaultChunk = 64;   // pixels per queue chunk
+constexpr uint32_t kDefaultBandRows = 16;
+
+thread_local std::string tl_error;
+thread_local int tl_code = 0;
+thread_local FrbStats tl_stats = {};
+thread_local uint32_t tl_variant = FRB_KERNEL_AUTO;
+
+int fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    tl_error = buf;
+    tl_code = code;
+    return code;
+}
+
+#define CU(call)                                                                                        \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess)                                                                          \
+            return fail(FRB_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+struct StatSlot {
+    unsigned long long iterations;
+    unsigned long long lane_iterations;
+};
+
+struct Slot {
+    cudaEvent_t ev_start = nullptr, ev_iter = nullptr, ev_shade = nullptr, ev_end = nullptr;
+    StatSlot *host = nullptr;  // pinned
+    uint64_t pixels = 0;
+    uint32_t launches = 0;
+    uint32_t variant = 0;
+    bool shaded = false;
+};
+
+struct DeviceCtx {
+    int dev = -1;
+    bool ready = false;
+    int sm_count = 0;
+    int iter_blocks_per_sm[2] = {0, 0};  // FORM 6, FORM 7
+    cudaStream_t stream = nullptr;       // the library's own stream for this device
+    cudaEvent_t ev_guard = nullptr;      // completion of the last render that used the shared raw buffers
+    cudaStream_t last_stream = nullptr;
+    bool have_guard = false;
+    std::mutex mu;
+    // grow-only device buffers
+    double *tab = nullptr;
+    size_t tab_cap = 0;  // doubles
+    uint32_t *iters = nullptr;
+    size_t iters_cap = 0;  // elements
+    double2 *zfinal = nullptr;
+    size_t z_cap = 0;
+    uint8_t *out = nullptr;
+    size_t out_cap = 0;  // bytes
+    unsigned int *queue = nullptr;
+    unsigned long long *stats = nullptr;
+    Slot slots[kSlots];
+    uint32_t next_slot = 0;
+};
+
+std::mutex g_mu;
+DeviceCtx *g_ctx[kMaxDevices] = {};
+int g_device_count = -1;
+uint32_t g_device_mask = 0;  // devices chosen by frb_init (0 = not initialised)
+
+int device_count_locked()
+{
+    if (g_device_count < 0) {
+        int n = 0;
+        cudaError_t e = cudaGetDeviceCount(&n);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            n = 0;
+        }
+        g_device_count = std::min(n, kMaxDevices);
+    }
+    return g_device_count;
+}
+
+int ctx_init(DeviceCtx *c, int dev)
+{
+    CU(cudaSetDevice(dev));
+    c->dev = dev;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major < 10)
+        return fail(FRB_ERR_NO_DEVICE, "device %d is sm_%d%d; this library carries sm_100a code only", dev, prop.major, prop.minor);
+    c->sm_count = prop.multiProcessorCount;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&c->ev_guard, cudaEventDisableTiming));
+    CU(cudaMalloc(&c->queue, 256));
+    CU(cudaMalloc(&c->stats, 256));
+    for (auto &s : c->slots) {
+        CU(cudaEventCreate(&s.ev_start));
+        CU(cudaEventCreate(&s.ev_iter));
+        CU(cudaEventCreate(&s.ev_shade));
+        CU(cudaEventCreate(&s.ev_end));
+        CU(cudaMallocHost(&s.host, sizeof(StatSlot)));
+        memset(s.host, 0, sizeof(StatSlot));
+    }
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->iter_blocks_per_sm[0], frb::frb_iterate_stream_kernel<6>,
+                                                     frb::kIterateThreads, 0));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->iter_blocks_per_sm[1], frb::frb_iterate_stream_kernel<7>,
+                                                     frb::kIterateThreads, 0));
+    if (c->iter_blocks_per_sm[0] < 1 || c->iter_blocks_per_sm[1] < 1)
+        return fail(FRB_ERR_CUDA, "iterate kernel does not fit on device %d", dev);
+    c->ready = true;
+    return FRB_OK;
+}
+
+void ctx_destroy(DeviceCtx *c)
+{
+    if (!c) return;
+    if (c->dev >= 0 && cudaSetDevice(c->dev) == cudaSuccess) {
+        cudaDeviceSynchronize();
+        cudaFree(c->tab);
+        cudaFree(c->iters);
+        cudaFree(c->zfinal);
+        cudaFree(c->out);
+        cudaFree(c->queue);
+        cudaFree(c->stats);
+        for (auto &s : c->slots) {
+            if (s.ev_start) cudaEventDestroy(s.ev_start);
+            if (s.ev_iter) cudaEventDestroy(s.ev_iter);
+            if (s.ev_shade) cudaEventDestroy(s.ev_shade);
+            if (s.ev_end) cudaEventDestroy(s.ev_end);
+            if (s.host) cudaFreeHost(s.host);
+        }
+        if (c->ev_guard) cudaEventDestroy(c->ev_guard);
+        if (c->stream) cudaStreamDestroy(c->stream);
+    }
+    delete c;
+}
+
+// Returns the (lazily created) context of `dev`, or nullptr with the error set.
+DeviceCtx *get_ctx(int dev)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    const int n = device_count_locked();
+    if (n == 0) {
+        fail(FRB_ERR_NO_DEVICE, "no usable CUDA device (cudaGetDeviceCount found none); this library has no CPU path");
+        return nullptr;
+    }
+    if (dev < 0 || dev >= n) {
+        fail(FRB_ERR_INVALID, "device %d out of range [0, %d)", dev, n);
+        return nullptr;
+    }
+    if (!g_ctx[dev]) {
+        DeviceCtx *c = new DeviceCtx();
+        if (ctx_init(c, dev) != FRB_OK) {
+            const std::string keep = tl_error;
+            const int code = tl_code;
+            ctx_destroy(c);
+            tl_error = keep;
+            tl_code = code;
+            return nullptr;
+        }
+        g_ctx[dev] = c;
+    }
+    return g_ctx[dev];
+}
+
+template <typename T>
+int ensure(T *&ptr, size_t &cap, size_t need)
+{
+    if (need <= cap) return FRB_OK;
+    if (ptr) CU(cudaFree(ptr));
+    ptr = nullptr;
+    cap = 0;
+    const size_t want = need + need / 8 + 1024;  // a little head-room so interactive resizes do not thrash
+    CU(cudaMalloc(&ptr, want * sizeof(T)));
+    cap = want;
+    return FRB_OK;
+}
+
+uint64_t double_bits(double v)
+{
+    uint64_t b;
+    memcpy(&b, &v, sizeof b);
+    return b;
+}
+
+FrbShard whole_frame()
+{
+    FrbShard s = {0u, 1u, 0u, 0u};
+    return s;
+}
+
+bool shard_valid(const FrbShard &s) { return s.count >= 1 && s.index < s.count; }
+
+uint32_t shard_band_rows(uint32_t height, const FrbShard &s)
+{
+    if (s.band_rows == 0) return std::max(height, 1u);
+    return s.band_rows;
+}
+
+uint32_t shard_rows(uint32_t height, const FrbShard &s)
+{
+    if (!shard_valid(s)) return 0;
+    const uint64_t br = shard_band_rows(height, s);
+    const uint64_t nbands = (height + br - 1) / br;  // bands in the image
+    uint64_t rows = 0;
+    if (nbands > s.index) {
+        const uint64_t mine = (nbands - s.index + s.count - 1) / s.count;  // bands k = index, index+count, ...
+        rows = mine * br;
+        const uint64_t last_band = s.index + (mine - 1) * s.count;
+        const uint64_t last_end = (last_band + 1) * br;
+        if (last_end > height) rows -= (last_end - height);
+    }
+    return (uint32_t)rows;
+}
+
+uint32_t shard_row_to_y(uint32_t height, const FrbShard &s, uint32_t lr)
+{
+    const uint32_t br = shard_band_rows(height, s);
+    const uint32_t band = lr / br;
+    return (band * s.count + s.index) * br + (lr - band * br);
+}
+
+// coord_to_space on the host with the same operation order as the device table kernel (used only to decide
+// which iteration form is provably exact; never to produce pixels).
+double host_coord(double coord, double max, double offset, double pos, double scale)
+{
+    volatile double a = coord / max;
+    volatile double b = a - offset;
+    volatile double c = b / scale;
+    volatile double d = c + pos;
+    return d;
+}
+
+// FORM 6 (p = x*y; nim = fma(p, 2, c.im)) differs from the reference's (2x*y) + c.im only when x*y is subnormal
+// or 2*x*y overflows.  It is selected only when neither can alter a result bit (see frb_kernels.cuh).
+bool form6_is_exact(const FrbConfig &cfg)
+{
+    const double S = cfg.limit * cfg.limit;
+    if (!(S <= 1e300)) return false;  // also rejects NaN and inf
+    const double tiny = 0x1p-900, huge = 1e150;
+    const double wf = (double)cfg.width, hf = (double)cfg.height;
+    // start points must not overflow x*y on the very first product
+    const double re_a = host_coord(0.0, hf, (wf / hf) / 2.0, cfg.pos.re, cfg.scale.re);
+    const double re_b = host_coord((double)(cfg.width ? cfg.width - 1 : 0), hf, (wf / hf) / 2.0, cfg.pos.re, cfg.scale.re);
+    const double im_a = host_coord(0.0, hf, 0.5, cfg.pos.im, cfg.scale.im);
+    const double im_b = host_coord((double)(cfg.height ? cfg.height - 1 : 0), hf, 0.5, cfg.pos.im, cfg.scale.im);
+    const double ext[4] = {re_a, re_b, im_a, im_b};
+    for (double v : ext)
+        if (!(std::fabs(v) <= huge)) return false;
+    if (cfg.algo == FRB_ALGO_JULIA) {
+        if (!(std::fabs(cfg.julia_set.re) <= huge) || !(std::fabs(cfg.julia_set.im) <= huge)) return false;
+        return std::fabs(cfg.julia_set.im) >= tiny;  // c.im == 0 lets im(z) decay through the subnormals: use FORM 7
+    }
+    // Mandelbrot: c.im = im0(y).  Exactly 0 is fine (im(z) stays 0); a non-zero |im0| < 2^-900 is not.
+    // im0 is monotone in y, so the smallest non-zero magnitude sits next to the sign change.
+    if ((im_a > 0.0) == (im_b > 0.0) && im_a != 0.0 && im_b != 0.0)
+        return std::min(std::fabs(im_a), std::fabs(im_b)) >= tiny;
+    for (uint32_t y = 0; y < cfg.height; ++y) {
+        const double v = std::fabs(host_coord((double)y, hf, 0.5, cfg.pos.im, cfg.scale.im));
+        if (v != 0.0 && !(v >= tiny)) return false;
+    }
+    return true;
+}
+
+struct Plan {
+    RenderParams p;
+    uint32_t variant;
+    uint64_t npix;
+    size_t out_bytes;
+};
+
+int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t format, Plan *plan)
+{
+    if (!shard_valid(sh)) return fail(FRB_ERR_INVALID, "bad shard: index %u of count %u", sh.index, sh.count);
+    if (format != 0 && format != FRB_RGB24 && format != FRB_RGBA32) return fail(FRB_ERR_INVALID, "unknown pixel format %u", format);
+    if (cfg.algo > FRB_ALGO_JULIA) return fail(FRB_ERR_INVALID, "unknown algo %u", cfg.algo);
+    RenderParams &p = plan->p;
+    memset(&p, 0, sizeof p);
+    p.width = cfg.width;
+    p.height = cfg.height;
+    p.rows = shard_rows(cfg.height, sh);
+    p.band_rows = shard_band_rows(cfg.height, sh);
+    p.shard_index = sh.index;
+    p.shard_count = sh.count;
+    p.iterations = cfg.iterations;
+    p.algo = cfg.algo;
+    // `let squared = limit * limit` (calc/src/lib.rs:246): one IEEE multiply, same on host and device
+    {
+        volatile double l = cfg.limit;
+        volatile double s = l * l;
+        p.limit_sq = s;
+    }
+    p.filter_hi = (uint32_t)(double_bits(p.limit_sq * 0.5) >> 32);
+    p.chunk = kDefaultChunk;
+    p.chunks_per_row = cfg.width ? (cfg.width + p.chunk - 1) / p.chunk : 0;
+    const uint64_t npix = (uint64_t)p.rows * cfg.width;
+    const uint64_t chunks = (uint64_t)p.rows * p.chunks_per_row;
+    if (npix > 0xfffffff0ull || chunks > 0xfffffff0ull)
+        return fail(FRB_ERR_TOO_LARGE, "shard of %u x %u pixels exceeds 2^32 pixels per launch; use more shards", cfg.width, p.rows);
+    p.total_chunks = (uint32_t)chunks;
+    p.julia_re = cfg.julia_set.re;
+    p.julia_im = cfg.julia_set.im;
+    p.pos_re = cfg.pos.re;
+    p.pos_im = cfg.pos.im;
+    p.scale_re = cfg.scale.re;
+    p.scale_im = cfg.scale.im;
+    p.stable_limit = cfg.stable_limit;
+    p.exposure = cfg.exposure;
+    p.smooth = cfg.smooth ? 1u : 0u;
+    p.inside = cfg.inside ? 1u : 0u;
+    p.primary = (uint32_t)cfg.primary_color.r | ((uint32_t)cfg.primary_color.g << 8) | ((uint32_t)cfg.primary_color.b << 16);
+    p.secondary = (uint32_t)cfg.secondary_color.r | ((uint32_t)cfg.secondary_color.g << 8) | ((uint32_t)cfg.secondary_color.b << 16);
+    p.format = format;
+    plan->npix = npix;
+    plan->out_bytes = (size_t)npix * format;
+    uint32_t v = tl_variant;
+    if (v == FRB_KERNEL_AUTO) v = form6_is_exact(cfg) ? FRB_KERNEL_STREAM6 : FRB_KERNEL_STREAM7;
+    plan->variant = v;
+
+    if (int rc = ensure(c.tab, c.tab_cap, (size_t)cfg.width + cfg.height + 2)) return rc;
+    if (int rc = ensure(c.iters, c.iters_cap, (size_t)npix + 4)) return rc;
+    if (int rc = ensure(c.zfinal, c.z_cap, (size_t)npix + 4)) return rc;
+    p.tab_re = c.tab;
+    p.tab_im = c.tab + cfg.width;
+    p.iters = c.iters;
+    p.zfinal = c.zfinal;
+    p.queue = c.queue;
+    p.stats = c.stats;
+    return FRB_OK;
+}
+
+// Enqueues tables -> iterate -> shade (if format != 0) on `st`.  Caller holds c.mu and has set the device.
+int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **slot_out)
+{
+    RenderParams &p = plan.p;
+    p.out = dev_out;
+    Slot &slot = c.slots[c.next_slot];
+    c.next_slot = (c.next_slot + 1) % kSlots;
+    slot.pixels = plan.npix;
+    slot.launches = 0;
+    slot.variant = plan.variant;
+    slot.shaded = false;
+    slot.host->iterations = 0;
+    slot.host->lane_iterations = 0;
+    *slot_out = &slot;
+
+    // the raw buffers (tables, counts, final z, queue) are shared by all renders of this device: order streams
+    if (c.have_guard && c.last_stream != st) CU(cudaStreamWaitEvent(st, c.ev_guard, 0));
+
+    CU(cudaEventRecord(slot.ev_start, st));
+    if (plan.npix > 0) {
+        const uint32_t n = std::max(p.width, p.height);
+        frb::frb_coord_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
+        slot.launches++;
+        if (p.algo != FRB_ALGO_BARNSLEY_FERN) {
+            if (plan.variant == FRB_KERNEL_SIMPLE) {
+                dim3 grid(p.rows, (p.width + 255) / 256);
+                frb::frb_iterate_simple_kernel<<<grid, 256, 0, st>>>(p);
+            } else {
+                const int form_idx = (plan.variant == FRB_KERNEL_STREAM7) ? 1 : 0;
+                const uint32_t warps_per_block = frb::kIterateThreads / 32;
+                uint32_t blocks = (uint32_t)(c.sm_count * c.iter_blocks_per_sm[form_idx]);
+                const uint32_t needed = (p.total_chunks + warps_per_block - 1) / warps_per_block;
+                blocks = std::max(1u, std::min(blocks, needed));
+                if (form_idx == 0)
+                    frb::frb_iterate_stream_kernel<6><<<blocks, frb::kIterateThreads, 0, st>>>(p);
+                else
+                    frb::frb_iterate_stream_kernel<7><<<blocks, frb::kIterateThreads, 0, st>>>(p);
+            }
+            slot.launches++;
+        } else {
+            // get_recursive_pixel returns BLACK without iterating (calc/src/lib.rs:211); keep the raw outputs defined
+            CU(cudaMemsetAsync(p.iters, 0, plan.npix * sizeof(uint32_t), st));
+            CU(cudaMemsetAsync(p.zfinal, 0, plan.npix * sizeof(double2), st));
+        }
+    }
+    CU(cudaEventRecord(slot.ev_iter, st));
+    if (plan.npix > 0 && p.format != 0) {
+        const uint64_t cta_px = (uint64_t)frb::kShadeThreads * frb::kShadePxPerThread;
+        const uint64_t nblocks = (plan.npix + cta_px - 1) / cta_px;
+        const uint32_t grid = (uint32_t)std::min<uint64_t>(nblocks, (uint64_t)c.sm_count * 32);
+        frb::frb_shade_kernel<<<grid, frb::kShadeThreads, 0, st>>>(p);
+        slot.launches++;
+        slot.shaded = true;
+    }
+    CU(cudaEventRecord(slot.ev_shade, st));
+    if (plan.npix > 0) CU(cudaMemcpyAsync(slot.host, c.stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, st));
+    CU(cudaGetLastError());
+    return FRB_OK;
+}
+
+int finish_enqueue(DeviceCtx &c, Slot &slot, cudaStream_t st)
+{
+    CU(cudaEventRecord(slot.ev_end, st));
+    CU(cudaEventRecord(c.ev_guard, st));
+    c.have_guard = true;
+    c.last_stream = st;
+    return FRB_OK;
+}
+
+int harvest(DeviceCtx &c, Slot &slot, FrbStats *out, double total_ms)
+{
+    (void)c;
+    CU(cudaEventSynchronize(slot.ev_end));
+    FrbStats s = {};
+    s.pixels = slot.pixels;
+    s.iterations = slot.host->iterations;
+    s.lane_iterations = slot.host->lane_iterations;
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, slot.ev_start, slot.ev_iter));
+    s.iterate_ms = ms;
+    CU(cudaEventElapsedTime(&ms, slot.ev_iter, slot.ev_shade));
+    s.shade_ms = ms;
+    CU(cudaEventElapsedTime(&ms, slot.ev_start, slot.ev_shade));
+    s.device_ms = ms;
+    s.total_ms = (float)total_ms;
+    s.kernel_launches = slot.launches;
+    s.devices = 1;
+    s.kernel_variant = slot.variant;
+    *out = s;
+    return FRB_OK;
+}
+
+double now_ms()
+{
+    using namespace std::chrono;
+    return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+// One blocking render of one shard on one device into a host buffer (RGB/RGBA) and/or raw host buffers.
+int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t format, uint8_t *host_out, size_t out_len,
+                    uint32_t *host_iters, double *host_z)
+{
+    const double t0 = now_ms();
+    DeviceCtx *c = get_ctx(dev);
+    if (!c) return tl_code;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(dev));
+    Plan plan;
+    if (int rc = make_plan(*c, cfg, sh, format, &plan)) return rc;
+    if (format != 0) {
+        if (out_len < plan.out_bytes) return fail(FRB_ERR_INVALID, "output buffer too small: %zu < %zu bytes", out_len, plan.out_bytes);
+        if (plan.out_bytes && !host_out) return fail(FRB_ERR_INVALID, "null output buffer");
+        if (int rc = ensure(c->out, c->out_cap, plan.out_bytes + 64)) return rc;
+    }
+    Slot *slot = nullptr;
+    if (int rc = enqueue(*c, plan, c->out, c->stream, &slot)) return rc;
+    if (plan.npix > 0) {
+        if (format != 0) CU(cudaMemcpyAsync(host_out, c->out, plan.out_bytes, cudaMemcpyDeviceToHost, c->stream));
+        if (host_iters) CU(cudaMemcpyAsync(host_iters, c->iters, plan.npix * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+        if (host_z) CU(cudaMemcpyAsync(host_z, c->zfinal, plan.npix * sizeof(double2), cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (int rc = finish_enqueue(*c, *slot, c->stream)) return rc;
+    CU(cudaStreamSynchronize(c->stream));
+    return harvest(*c, *slot, &tl_stats, now_ms() - t0);
+}
+
+struct AsyncRecord {
+    int dev = -1;
+    Slot *slot = nullptr;
+    double t0 = 0.0;
+};
+thread_local AsyncRecord tl_async_ring[kSlots];
+thread_local uint64_t tl_async_count = 0;
+
+std::vector<int> active_devices()
+{
+    std::vector<int> v;
+    int n;
+    uint32_t mask;
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        n = device_count_locked();
+        mask = g_device_mask;
+    }
+    for (int d = 0; d < n; ++d)
+        if (mask == 0 || (mask >> d) & 1u) v.push_back(d);
+    return v;
+}
+
+}  // namespace
+
+// ============================================================ C ABI ============================================================
+
+extern "C" {
+
+uint32_t frb_abi_version(void) { return FRB_ABI_VERSION; }
+
+const char *frb_last_error(void) { return tl_error.c_str(); }
+
+FrbRGB frb_rgb_new(uint8_t r, uint8_t b, uint8_t g)
+{
+    FrbRGB c;
+    c.r = r;
+    c.g = g;
+    c.b = b;
+    return c;
+}
+
+void frb_config_default(FrbConfig *cfg, uint32_t algo)
+{
+    if (!cfg) return;
+    memset(cfg, 0, sizeof *cfg);
+    const bool fern = (algo == FRB_ALGO_BARNSLEY_FERN);
+    cfg->algo = algo;
+    cfg->width = 2000;
+    cfg->height = 1000;
+    cfg->iterations = fern ? 10000000u : 50u;
+    cfg->limit = 65536.0;
+    cfg->stable_limit = 2.0;
+    cfg->scale.re = 0.4;
+    cfg->scale.im = 0.4;
+    cfg->exposure = 2.0;
+    cfg->inside = 1;
+    cfg->smooth = 1;
+    cfg->primary_color = fern ? frb_rgb_new(4, 100, 3) : frb_rgb_new(40, 40, 255);
+    cfg->secondary_color = fern ? frb_rgb_new(240, 240, 240) : frb_rgb_new(240, 170, 0);
+    cfg->color_weight = 0.01;
+}
+
+uint32_t frb_shard_rows(uint32_t height, const FrbShard *shard)
+{
+    const FrbShard s = shard ? *shard : whole_frame();
+    return shard_rows(height, s);
+}
+
+uint32_t frb_shard_row_to_y(uint32_t height, const FrbShard *shard, uint32_t local_row)
+{
+    const FrbShard s = shard ? *shard : whole_frame();
+    if (!shard_valid(s)) return 0;
+    return shard_row_to_y(height, s, local_row);
+}
+
+int frb_device_count(void)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    return device_count_locked();
+}
+
+int frb_init(uint32_t device_mask)
+{
+    int n = frb_device_count();
+    if (n == 0) return fail(FRB_ERR_NO_DEVICE, "no usable CUDA device; this library has no CPU path");
+    bool any = false;
+    for (int d = 0; d < n; ++d) {
+        if (device_mask != 0 && !((device_mask >> d) & 1u)) continue;
+        if (!get_ctx(d)) return tl_code;
+        any = true;
+    }
+    if (!any) return fail(FRB_ERR_INVALID, "device mask 0x%x selects none of the %d devices", device_mask, n);
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_device_mask = device_mask;
+    return FRB_OK;
+}
+
+void frb_shutdown(void)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (int d = 0; d < kMaxDevices; ++d) {
+        ctx_destroy(g_ctx[d]);
+        g_ctx[d] = nullptr;
+    }
+    g_device_mask = 0;
+}
+
+int frb_set_kernel_variant(uint32_t variant)
+{
+    if (variant > FRB_KERNEL_SIMPLE) return fail(FRB_ERR_INVALID, "unknown kernel variant %u", variant);
+    tl_variant = variant;
+    return FRB_OK;
+}
+
+int frb_render_shard(const FrbConfig *cfg, const FrbShard *shard, uint8_t *out, size_t out_len, uint32_t format, int device)
+{
+    if (!cfg) return fail(FRB_ERR_INVALID, "null config");
+    if (format != FRB_RGB24 && format != FRB_RGBA32) return fail(FRB_ERR_INVALID, "unknown pixel format %u", format);
+    const FrbShard s = shard ? *shard : whole_frame();
+    return render_blocking(*cfg, s, device, format, out, out_len, nullptr, nullptr);
+}
+
+int frb_render_counts(const FrbConfig *cfg, const FrbShard *shard, uint32_t *iters, double *zfinal, int device)
+{
+    if (!cfg) return fail(FRB_ERR_INVALID, "null config");
+    const FrbShard s = shard ? *shard : whole_frame();
+    if (!iters && (uint64_t)cfg->width * shard_rows(cfg->height, s) > 0) return fail(FRB_ERR_INVALID, "null iters buffer");
+    return render_blocking(*cfg, s, device < 0 ? 0 : device, 0, nullptr, 0, iters, zfinal);
+}
+
+int frb_render(const FrbConfig *cfg, uint8_t *out, size_t out_len, uint32_t format, int device)
+{
+    if (!cfg) return fail(FRB_ERR_INVALID, "null config");
+    if (format != FRB_RGB24 && format != FRB_RGBA32) return fail(FRB_ERR_INVALID, "unknown pixel format %u", format);
+    const size_t need = (size_t)cfg->width * cfg->height * format;
+    if (out_len < need) return fail(FRB_ERR_INVALID, "output buffer too small: %zu < %zu bytes", out_len, need);
+    if (device >= 0) return render_blocking(*cfg, whole_frame(), device, format, out, out_len, nullptr, nullptr);
+
+    // device = -1: interleaved 16-row bands over all initialised devices, one stream per device, strided gather
+    // straight into the caller's image.  No collective: shards are independent.
+    const std::vector<int> devs = active_devices();
+    if (devs.empty()) return fail(FRB_ERR_NO_DEVICE, "no usable CUDA device; this library has no CPU path");
+    if (devs.size() == 1 || cfg->height <= kDefaultBandRows)
+        return render_blocking(*cfg, whole_frame(), devs[0], format, out, out_len, nullptr, nullptr);
+
+    const double t0 = now_ms();
+    const uint32_t G = (uint32_t)devs.size();
+    struct Part {
+        DeviceCtx *c;
+        Slot *slot;
+        Plan plan;
+    };
+    std::vector<Part> parts(G);
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (uint32_t g = 0; g < G; ++g) {
+        parts[g].c = get_ctx(devs[g]);
+        if (!parts[g].c) return tl_code;
+        locks.emplace_back(parts[g].c->mu);
+    }
+    const size_t row_bytes = (size_t)cfg->width * format;
+    for (uint32_t g = 0; g < G; ++g) {
+        DeviceCtx &c = *parts[g].c;
+        CU(cudaSetDevice(c.dev));
+        FrbShard sh = {g, G, kDefaultBandRows, 0u};
+        if (int rc = make_plan(c, *cfg, sh, format, &parts[g].plan)) return rc;
+        if (int rc = ensure(c.out, c.out_cap, parts[g].plan.out_bytes + 64)) return rc;
+        if (int rc = enqueue(c, parts[g].plan, c.out, c.stream, &parts[g].slot)) return rc;
+        const uint32_t rows = parts[g].plan.p.rows;
+        if (rows > 0) {
+            // full bands: one strided copy; the (possibly partial) last band separately
+            const size_t band_bytes = row_bytes * kDefaultBandRows;
+            const uint32_t full = rows / kDefaultBandRows;
+            uint8_t *dst0 = out + (size_t)g * band_bytes;
+            if (full > 0)
+                CU(cudaMemcpy2DAsync(dst0, (size_t)G * band_bytes, c.out, band_bytes, band_bytes, full, cudaMemcpyDeviceToHost, c.stream));
+            const uint32_t rest = rows - full * kDefaultBandRows;
+            if (rest > 0)
+                CU(cudaMemcpyAsync(dst0 + (size_t)full * G * band_bytes, c.out + (size_t)full * band_bytes, (size_t)rest * row_bytes,
+                                   cudaMemcpyDeviceToHost, c.stream));
+        }
+        if (int rc = finish_enqueue(c, *parts[g].slot, c.stream)) return rc;
+    }
+    FrbStats total = {};
+    for (uint32_t g = 0; g < G; ++g) {
+        DeviceCtx &c = *parts[g].c;
+        CU(cudaSetDevice(c.dev));
+        CU(cudaStreamSynchronize(c.stream));
+        FrbStats s;
+        if (int rc = harvest(c, *parts[g].slot, &s, 0.0)) return rc;
+        total.pixels += s.pixels;
+        total.iterations += s.iterations;
+        total.lane_iterations += s.lane_iterations;
+        total.iterate_ms = std::max(total.iterate_ms, s.iterate_ms);
+        total.shade_ms = std::max(total.shade_ms, s.shade_ms);
+        total.device_ms = std::max(total.device_ms, s.device_ms);
+        total.kernel_launches += s.kernel_launches;
+        total.kernel_variant = s.kernel_variant;
+    }
+    total.devices = G;
+    total.total_ms = (float)(now_ms() - t0);
+    tl_stats = total;
+    return FRB_OK;
+}
+
+int frb_render_frames(const FrbConfig *cfgs, uint32_t n, uint8_t *out, size_t out_len, uint32_t format, int device)
+{
+    if (!cfgs && n) return fail(FRB_ERR_INVALID, "null configs");
+    if (format != FRB_RGB24 && format != FRB_RGBA32) return fail(FRB_ERR_INVALID, "unknown pixel format %u", format);
+    size_t need = 0;
+    for (uint32_t k = 0; k < n; ++k) need += (size_t)cfgs[k].width * cfgs[k].height * format;
+    if (out_len < need) return fail(FRB_ERR_INVALID, "output buffer too small: %zu < %zu bytes", out_len, need);
+    std::vector<int> devs;
+    if (device >= 0)
+        devs.push_back(device);
+    else
+        devs = active_devices();
+    if (devs.empty()) return fail(FRB_ERR_NO_DEVICE, "no usable CUDA device; this library has no CPU path");
+    const double t0 = now_ms();
+    // Frames are independent; frame k -> device k % G (round robin balances the 80x cost spread of a zoom to
+    // ~1.02).  Each device renders its frames in order on its own stream; the shared raw buffers
+    // are reused frame after frame (stream order protects them), each frame is copied out as soon as it is shaded.
+    const uint32_t G = (uint32_t)devs.size();
+    std::vector<DeviceCtx *> ctx(G);
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (uint32_t g = 0; g < G; ++g) {
+        ctx[g] = get_ctx(devs[g]);
+        if (!ctx[g]) return tl_code;
+        locks.emplace_back(ctx[g]->mu);
+    }
+    FrbStats total = {};
+    std::vector<size_t> offset(n);
+    size_t off = 0;
+    for (uint32_t k = 0; k < n; ++k) {
+        offset[k] = off;
+        off += (size_t)cfgs[k].width * cfgs[k].height * format;
+    }
+    // Frames of one device run back to back; statistics slots are harvested every kSlots frames at most.
+    std::vector<std::vector<Slot *>> pending(G);
+    auto drain = [&](uint32_t g) -> int {
+        DeviceCtx &c = *ctx[g];
+        CU(cudaSetDevice(c.dev));
+        for (Slot *s : pending[g]) {
+            FrbStats st;
+            if (int rc = harvest(c, *s, &st, 0.0)) return rc;
+            total.pixels += st.pixels;
+            total.iterations += st.iterations;
+            total.lane_iterations += st.lane_iterations;
+            total.iterate_ms += st.iterate_ms;
+            total.shade_ms += st.shade_ms;
+            total.device_ms += st.device_ms;
+            total.kernel_launches += st.kernel_launches;
+            total.kernel_variant = st.kernel_variant;
+        }
+        pending[g].clear();
+        return FRB_OK;
+    };
+    for (uint32_t k = 0; k < n; ++k) {
+        const uint32_t g = k % G;
+        DeviceCtx &c = *ctx[g];
+        if (pending[g].size() >= (size_t)kSlots - 1)
+            if (int rc = drain(g)) return rc;
+        CU(cudaSetDevice(c.dev));
+        Plan plan;
+        if (int rc = make_plan(c, cfgs[k], whole_frame(), format, &plan)) return rc;
+        if (int rc = ensure(c.out, c.out_cap, plan.out_bytes + 64)) return rc;
+        Slot *slot = nullptr;
+        if (int rc = enqueue(c, plan, c.out, c.stream, &slot)) return rc;
+        if (plan.out_bytes) CU(cudaMemcpyAsync(out + offset[k], c.out, plan.out_bytes, cudaMemcpyDeviceToHost, c.stream));
+        if (int rc = finish_enqueue(c, *slot, c.stream)) return rc;
+        pending[g].push_back(slot);
+    }
+    for (uint32_t g = 0; g < G; ++g)
+        if (int rc = drain(g)) return rc;
+    total.devices = G;
+    total.total_ms = (float)(now_ms() - t0);
+    tl_stats = total;
+    return FRB_OK;
+}
+
+int frb_render_device_async(const FrbConfig *cfg, const FrbShard *shard, void *dev_out, size_t out_len, uint32_t format, int device,
+                            void *stream)
+{
+    if (!cfg) return fail(FRB_ERR_INVALID, "null config");
+    if (format != FRB_RGB24 && format != FRB_RGBA32) return fail(FRB_ERR_INVALID, "unknown pixel format %u", format);
+    const FrbShard s = shard ? *shard : whole_frame();
+    DeviceCtx *c = get_ctx(device);
+    if (!c) return tl_code;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(device));
+    Plan plan;
+    if (int rc = make_plan(*c, *cfg, s, format, &plan)) return rc;
+    if (out_len < plan.out_bytes) return fail(FRB_ERR_INVALID, "output buffer too small: %zu < %zu bytes", out_len, plan.out_bytes);
+    if (plan.out_bytes && !dev_out) return fail(FRB_ERR_INVALID, "null device output buffer");
+    if (((uintptr_t)dev_out & 15u) != 0) return fail(FRB_ERR_INVALID, "device output buffer must be 16-byte aligned");
+    cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+    const double t0 = now_ms();
+    Slot *slot = nullptr;
+    if (int rc = enqueue(*c, plan, (uint8_t *)dev_out, st, &slot)) return rc;
+    if (int rc = finish_enqueue(*c, *slot, st)) return rc;
+    AsyncRecord &rec = tl_async_ring[tl_async_count % kSlots];
+    rec.dev = device;
+    rec.slot = slot;
+    rec.t0 = t0;
+    ++tl_async_count;
+    return FRB_OK;
+}
+
+int frb_async_stats(uint32_t back, FrbStats *stats)
+{
+    if (tl_async_count == 0) return fail(FRB_ERR_INVALID, "no asynchronous render issued on this thread");
+    if (back >= (uint32_t)kSlots / 2 || back >= tl_async_count)
+        return fail(FRB_ERR_INVALID, "statistics of the render %u calls ago are no longer kept (ring of %d)", back, kSlots / 2);
+    const AsyncRecord &rec = tl_async_ring[(tl_async_count - 1 - back) % kSlots];
+    DeviceCtx *c = get_ctx(rec.dev);
+    if (!c) return tl_code;
+    CU(cudaSetDevice(rec.dev));
+    FrbStats s;
+    if (int rc = harvest(*c, *rec.slot, &s, now_ms() - rec.t0)) return rc;
+    tl_stats = s;
+    if (stats) *stats = s;
+    return FRB_OK;
+}
+
+int frb_sync_stats(FrbStats *stats) { return frb_async_stats(0, stats); }
+
+int frb_last_stats(FrbStats *stats)
+{
+    if (!stats) return fail(FRB_ERR_INVALID, "null stats");
+    *stats = tl_stats;
+    return FRB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,451 @@
+// frb_kernels.cuh — device side of the B200 escape-time renderer (sm_100a only).
+//
+// The path being replaced (reference, /root/reference):
+//   calc/src/lib.rs:181-197  coord_to_space / xy_to_imaginary      -> frb_coord_tables_kernel
+//   calc/src/lib.rs:245-257  recursive (the z <- z^2 + c loop)     -> frb_iterate_stream_kernel / frb_iterate_simple_kernel
+//   calc/src/lib.rs:214-234  classify + smooth colour + palette    -> frb_shade_kernel
+//   calc/src/lib.rs:133-139  color_multiply (with the g/b swap)    -> shade_pixel()
+//   src/lib.rs:255-269       get_image row loop (rayon)            -> the persistent chunk queue
+//
+// All FP64 arithmetic on the result path uses the round-to-nearest intrinsics (__dadd_rn, __dmul_rn, __fma_rn,
+// __ddiv_rn, __dsqrt_rn), which nvcc never contracts or reassociates; the translation unit is additionally built
+// with -fmad=false.  Tensor cores and TMA are deliberately unused: the path is a scalar FP64 recurrence with a
+// data-dependent exit, bounded by the FP64 pipe (64 lanes / SM), not by HBM or by a contraction.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace frb {
+
+constexpr int kIterateThreads = 256;  // 8 warps per CTA; warps are fully independent (no smem, no CTA barrier)
+constexpr int kUnroll = 8;            // iterations per lock-step block between refill checks
+constexpr int kShadeThreads = 256;
+constexpr int kShadePxPerThread = 4;  // 4 px/thread -> one 16-byte RGBA store, 3 x 16-byte RGB stores per 4 threads
+
+enum : uint32_t { kAlgoMandelbrot = 0, kAlgoFern = 1, kAlgoJulia = 2 };
+
+// Everything a launch needs, passed by value (__grid_constant__ -> constant bank, uniform loads).
+struct RenderParams {
+    // geometry of this launch: `rows` compact local rows of a shard, each `width` pixels
+    uint32_t width;
+    uint32_t height;
+    uint32_t rows;
+    uint32_t band_rows;    // >= 1
+    uint32_t shard_index;
+    uint32_t shard_count;  // >= 1
+    uint32_t iterations;
+    uint32_t algo;
+    // escape test
+    double limit_sq;       // S = limit * limit (calc/src/lib.rs:246)
+    uint32_t filter_hi;    // high word of S/2: max(hi(re^2), hi(im^2)) >= filter_hi is necessary for re^2+im^2 > S
+    uint32_t chunk;        // pixels per queue chunk (a segment of one row)
+    uint32_t chunks_per_row;
+    uint32_t total_chunks;
+    double julia_re, julia_im;
+    // coordinate map inputs (calc/src/lib.rs:181-197)
+    double pos_re, pos_im, scale_re, scale_im;
+    // colour (calc/src/lib.rs:214-234)
+    double stable_limit, exposure;
+    uint32_t smooth, inside;
+    uint32_t primary;      // stored fields r | g<<8 | b<<16
+    uint32_t secondary;
+    uint32_t format;       // 3 = RGB24, 4 = RGBA32
+    uint32_t pad0;
+    // buffers
+    double *tab_re;              // [width]   re0(x)
+    double *tab_im;              // [height]  im0(y), indexed by IMAGE row
+    uint32_t *iters;             // [rows*width] count returned by recursive()
+    double2 *zfinal;             // [rows*width] position returned by recursive()
+    uint8_t *out;                // [rows*width*format]
+    unsigned int *queue;         // chunk counter
+    unsigned long long *stats;   // [0] useful iterations, [1] lane-slot iterations issued (32 x warp trips x unroll)
+};
+
+// local (compact) row of a shard -> image row; see FrbShard in include/frb.h
+__device__ __forceinline__ uint32_t local_row_to_y(const RenderParams &p, uint32_t lr)
+{
+    const uint32_t band = lr / p.band_rows;
+    const uint32_t r = lr - band * p.band_rows;
+    return (band * p.shard_count + p.shard_index) * p.band_rows + r;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K0: coordinate tables.  re0 depends on x only and im0 on y only (calc/src/lib.rs:194-195), so W+H values
+// computed once with the reference's exact operation order replace 4 divisions per pixel.  Also resets the
+// work queue and the statistics (stream-ordered before the iterate kernel).
+// ---------------------------------------------------------------------------------------------------------
+__global__ void frb_coord_tables_kernel(const __grid_constant__ RenderParams p)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t == 0) {
+        *p.queue = 0u;
+        p.stats[0] = 0ull;
+        p.stats[1] = 0ull;
+    }
+    const double wf = (double)p.width, hf = (double)p.height;
+    if (t < p.width) {
+        // coord_to_space(x, height, (width/height)/2.0, pos.re, scale.re)
+        const double off = __ddiv_rn(__ddiv_rn(wf, hf), 2.0);
+        const double v = __ddiv_rn(__dsub_rn(__ddiv_rn((double)t, hf), off), p.scale_re);
+        p.tab_re[t] = __dadd_rn(v, p.pos_re);
+    }
+    if (t < p.height) {
+        // coord_to_space(y, height, 0.5, pos.im, scale.im)
+        const double v = __ddiv_rn(__dsub_rn(__ddiv_rn((double)t, hf), 0.5), p.scale_im);
+        p.tab_im[t] = __dadd_rn(v, p.pos_im);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// One iteration, two formulations.
+// ---------------------------------------------------------------------------------------------------------
+
+// Per-lane orbit state.  (x, y) = z_k; (a, b) = (x*x, y*y) carried from the previous escape test (stream kernels).
+struct Orbit {
+    double x, y, a, b, cr, ci;
+};
+
+// Reference order exactly as written (calc/src/lib.rs:88-89, 103-104, 95, 251): 6 mul + 4 add + 1 compare.
+// Returns true when `next.squared_distance() > squared`; (x, y) is `next` afterwards either way.
+__device__ __forceinline__ bool step_exact(Orbit &o, const double S)
+{
+    const double a = __dmul_rn(o.x, o.x);
+    const double b = __dmul_rn(o.y, o.y);
+    double nre = __dsub_rn(a, b);
+    const double t = __dmul_rn(2.0, o.x);
+    double nim = __dmul_rn(t, o.y);
+    nre = __dadd_rn(nre, o.cr);
+    nim = __dadd_rn(nim, o.ci);
+    o.x = nre;
+    o.y = nim;
+    const double d = __dadd_rn(__dmul_rn(nre, nre), __dmul_rn(nim, nim));
+    return d > S;
+}
+
+// The streaming formulation: the two squares of squared_distance() are carried into the next iteration's
+// square() (they are the same roundings of the same operands), and the sum d = a' + b' with its compare is only
+// evaluated when an integer-pipe filter fires:
+//   max(hi32(a'), hi32(b')) >= hi32(S/2)   is NECESSARY for   a' + b' > S
+// (a', b' are squares, so non-negative or NaN; if both are < S/2 the exact sum is < S and rounding is monotone;
+// the unsigned compare of the high words also fires for +inf and NaN, and the exact test then decides exactly as
+// the reference would).  That leaves per iteration:
+//   s   = a - b            (re*re) - (im*im)                                   DADD
+//   nre = s + cr           + c.re                                               DADD
+//   a'  = nre * nre ; b' = nim * nim                                            2 x DMUL
+// and for the imaginary part either
+//   FORM 7 (exact for ANY input):  t = x + x (== 2.0*x, exact) ; q = t * y ; nim = q + ci        DADD DMUL DADD
+//   FORM 6:  p = x * y ; nim = fma(p, 2.0, ci)                                                   DMUL DFMA
+//     2*p is exact, so the fma rounds 2*round(x*y) + ci once; 2*round(x*y) == round((2x)*y) unless x*y is
+//     subnormal or overflows.  The host (frb_api.cu: form6_is_exact) only selects FORM 6 when neither can change a
+//     result bit: S <= 1e300 and |c.im| is either 0 with im(z) == 0 forever (Mandelbrot real-axis row) or
+//     >= 2^-900 (then a subnormal x*y is far below half an ulp of c.im and both forms round to the same value).
+// 6 is the floor for bit-exactness: the reference performs six roundings per iteration whose results are all
+// live (a-b, +c.re, 2xy, +c.im, re^2, im^2) and every FP64 instruction delivers exactly one.
+template <int FORM>
+__device__ __forceinline__ void stream_core(Orbit &o)
+{
+    const double s = __dsub_rn(o.a, o.b);
+    double nim;
+    if (FORM == 6) {
+        const double p = __dmul_rn(o.x, o.y);
+        nim = __fma_rn(p, 2.0, o.ci);
+    } else {
+        const double t = __dadd_rn(o.x, o.x);
+        nim = __dadd_rn(__dmul_rn(t, o.y), o.ci);
+    }
+    const double nre = __dadd_rn(s, o.cr);
+    o.x = nre;
+    o.y = nim;
+    o.a = __dmul_rn(nre, nre);
+    o.b = __dmul_rn(nim, nim);
+}
+
+// integer-pipe escape filter (necessary condition, see above)
+__device__ __forceinline__ bool stream_filter(const Orbit &o, const uint32_t filter_hi)
+{
+    const uint32_t ha = (uint32_t)__double2hiint(o.a);
+    const uint32_t hb = (uint32_t)__double2hiint(o.b);
+    return max(ha, hb) >= filter_hi;
+}
+
+// the reference's test, `next.squared_distance() > squared` (calc/src/lib.rs:250-251), on the carried squares
+__device__ __forceinline__ bool stream_escaped(const Orbit &o, const double S)
+{
+    return __dadd_rn(o.a, o.b) > S;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K1: persistent lane-refill iterate kernel.
+//
+// Grid = SMs x resident CTAs; every WARP is an independent worker.  Work units are chunks (segments of one
+// image row, p.chunk pixels) handed out by one global atomic counter; the id of the next chunk is prefetched
+// so the atomic's latency is hidden behind iteration blocks.  Each lane owns one pixel's orbit in registers.
+// The warp runs kUnroll iterations in lock step, then (warp-uniform ballot) lanes whose pixel finished store
+// its raw result (count, final z: 20 B) and take the next pixel of the warp's chunk cursor.  Lanes therefore
+// never wait for the slowest pixel of a tile: utilisation of the FP64 pipe is bounded by the U/2 iterations a
+// finished lane idles until the next refill point, not by the spread of escape times inside a warp.
+// Colour is NOT computed here (its sqrt/log2 would run at 1/32 lane efficiency); frb_shade_kernel does it at full
+// efficiency from the raw results, which also gives the parity hook (frb_render_counts) for free.
+// ---------------------------------------------------------------------------------------------------------
+template <int FORM>
+__global__ void __launch_bounds__(kIterateThreads, 4)
+frb_iterate_stream_kernel(const __grid_constant__ RenderParams p)
+{
+    constexpr unsigned FULL = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+
+    const double S = p.limit_sq;
+    const uint32_t filter_hi = p.filter_hi;
+    const uint32_t iterations = p.iterations;
+    const bool julia = (p.algo == kAlgoJulia);
+
+    Orbit o = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    uint32_t i = 0;       // iterations already executed for the lane's pixel
+    uint32_t pix = 0;     // compact pixel index (output slot)
+    bool active = false;
+
+    // warp-uniform chunk cursor
+    uint32_t cur_x = 0, cur_end = 0, cur_rowpix = 0;
+    double cur_im = 0.0;
+    bool drained = false;
+    // prefetched id of the next chunk (meaningful on lane 0)
+    uint32_t next_chunk = 0;
+    if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
+
+    unsigned long long useful = 0;  // loop-body executions of finished pixels (per lane)
+    uint32_t trips = 0;             // lock-step blocks issued by this warp
+
+    for (;;) {
+        unsigned need = __ballot_sync(FULL, !active);
+        if (need != 0u) {
+            while (!drained && need != 0u) {
+                if (cur_x == cur_end) {
+                    const uint32_t c = __shfl_sync(FULL, next_chunk, 0);
+                    if (c >= p.total_chunks) {
+                        drained = true;
+                        break;
+                    }
+                    if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
+                    const uint32_t lr = c / p.chunks_per_row;
+                    const uint32_t seg = c - lr * p.chunks_per_row;
+                    cur_x = seg * p.chunk;
+                    cur_end = min(cur_x + p.chunk, p.width);
+                    cur_rowpix = lr * p.width;
+                    cur_im = __ldg(p.tab_im + local_row_to_y(p, lr));
+                }
+                const uint32_t avail = cur_end - cur_x;
+                const uint32_t rank = __popc(need & lt_mask);
+                if (!active && rank < avail) {
+                    const uint32_t px = cur_x + rank;
+                    const double re0 = __ldg(p.tab_re + px);
+                    // get_recursive_pixel (calc/src/lib.rs:208-210): Mandelbrot c = start, Julia c = julia_set
+                    o.x = re0;
+                    o.y = cur_im;
+                    o.cr = julia ? p.julia_re : re0;
+                    o.ci = julia ? p.julia_im : cur_im;
+                    o.a = __dmul_rn(re0, re0);
+                    o.b = __dmul_rn(cur_im, cur_im);
+                    i = 0;
+                    pix = cur_rowpix + px;
+                    active = true;
+                }
+                cur_x += min((uint32_t)__popc(need), avail);
+                need = __ballot_sync(FULL, !active);
+            }
+            if (need == FULL) break;  // queue drained and no lane holds a pixel
+        }
+
+        ++trips;
+        if (active) {
+            const uint32_t rem = iterations - i;
+            bool done = false;
+            uint32_t count = iterations;
+            if (rem >= (uint32_t)kUnroll) {
+                // hot path: kUnroll x (6|7 FP64 + filter + branch); the exact test lives on the cold path only
+                uint32_t k = 0;
+                bool cand = false;
+#pragma unroll
+                for (int u = 0; u < kUnroll; ++u) {
+                    stream_core<FORM>(o);
+                    if (stream_filter(o, filter_hi)) {
+                        k = (uint32_t)u;
+                        cand = true;
+                        break;
+                    }
+                }
+                if (cand) {
+                    // cold path: finish this block one step at a time with the exact test after every step
+                    for (;;) {
+                        if (stream_escaped(o, S)) {
+                            count = i + k;
+                            done = true;
+                            break;
+                        }
+                        if (++k == (uint32_t)kUnroll) break;
+                        stream_core<FORM>(o);
+                    }
+                }
+                i += (uint32_t)kUnroll;
+            } else {
+                // fewer than kUnroll iterations left: finish the pixel here
+                done = true;
+                for (uint32_t k = 0; k < rem; ++k) {
+                    stream_core<FORM>(o);
+                    if (stream_filter(o, filter_hi) && stream_escaped(o, S)) {
+                        count = i + k;
+                        break;
+                    }
+                }
+            }
+            if (done) {
+                // recursive() returns (next, i) on escape, (previous, iterations) otherwise: (o.x, o.y) is that position
+                p.iters[pix] = count;
+                p.zfinal[pix] = make_double2(o.x, o.y);
+                useful += (count < iterations) ? (unsigned long long)count + 1ull : (unsigned long long)iterations;
+                active = false;
+            }
+        }
+    }
+
+    // statistics: one atomic per warp
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) useful += __shfl_xor_sync(FULL, useful, s);
+    if (lane == 0) {
+        atomicAdd(p.stats + 0, useful);
+        atomicAdd(p.stats + 1, (unsigned long long)trips * (unsigned long long)(32 * kUnroll));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K1s: cross-check kernel — one thread per pixel, reference order as written, no queue, no refill.
+// Lock-step warps of 32x1 pixels, so slower than the stream kernels; used to validate the stream kernels at full
+// frame sizes where the CPU oracle would need minutes, and available as FRB_KERNEL_SIMPLE.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+frb_iterate_simple_kernel(const __grid_constant__ RenderParams p)
+{
+    // blockIdx.x = local row (x dimension allows 2^31-1 rows), blockIdx.y = column block
+    const uint32_t x = blockIdx.y * blockDim.x + threadIdx.x;
+    const uint32_t lr = blockIdx.x;
+    const bool valid = (x < p.width) && (lr < p.rows);
+    unsigned long long useful = 0;
+    if (valid) {
+        const double re0 = p.tab_re[x];
+        const double im0 = p.tab_im[local_row_to_y(p, lr)];
+        const bool julia = (p.algo == kAlgoJulia);
+        Orbit o = {re0, im0, 0.0, 0.0, julia ? p.julia_re : re0, julia ? p.julia_im : im0};
+        const double S = p.limit_sq;
+        uint32_t count = p.iterations;
+        for (uint32_t i = 0; i < p.iterations; ++i) {
+            if (step_exact(o, S)) {
+                count = i;
+                break;
+            }
+        }
+        const uint32_t pix = lr * p.width + x;
+        p.iters[pix] = count;
+        p.zfinal[pix] = make_double2(o.x, o.y);
+        useful = (count < p.iterations) ? (unsigned long long)count + 1ull : (unsigned long long)p.iterations;
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) useful += __shfl_xor_sync(0xffffffffu, useful, s);
+    if ((threadIdx.x & 31u) == 0 && useful != 0ull) atomicAdd(p.stats + 0, useful);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K2: shade.  Raw (count, final z) -> colour, at full lane efficiency, 16-byte coalesced stores.
+// ---------------------------------------------------------------------------------------------------------
+
+// Rust `f64 as u8`: truncate toward zero, saturate, NaN -> 0.  cvt.rzi.u32.f64 saturates and maps NaN to 0.
+__device__ __forceinline__ uint32_t sat_u8(double v)
+{
+    return min(__double2uint_rz(v), 255u);
+}
+
+// color_multiply (calc/src/lib.rs:133-139): RGB::new(r*m, g*m, b*m) with new(r, b, g) => out.g = b*m, out.b = g*m.
+__device__ __forceinline__ uint32_t color_multiply(uint32_t stored, double m)
+{
+    const double cr = (double)(stored & 0xffu);
+    const double cg = (double)((stored >> 8) & 0xffu);
+    const double cb = (double)((stored >> 16) & 0xffu);
+    const uint32_t out_r = sat_u8(__dmul_rn(cr, m));
+    const uint32_t out_b = sat_u8(__dmul_rn(cg, m));  // second ctor argument lands in .b
+    const uint32_t out_g = sat_u8(__dmul_rn(cb, m));  // third ctor argument lands in .g
+    return out_r | (out_g << 8) | (out_b << 16);
+}
+
+// get_recursive_pixel after recursive() (calc/src/lib.rs:214-234).  Returns r | g<<8 | b<<16.
+__device__ __forceinline__ uint32_t shade_pixel(const RenderParams &p, uint32_t count, double2 z)
+{
+    if (p.algo == kAlgoFern) return 0u;  // `_ => return RGB::BLACK`
+    const double dist = __dadd_rn(__dmul_rn(z.x, z.x), __dmul_rn(z.y, z.y));
+    if (dist > p.stable_limit) {
+        double it = (double)count;
+        if (p.smooth) {
+            const double log_zn = __ddiv_rn(log2(__dsqrt_rn(dist)), 2.0);
+            const double nu = log2(log_zn);
+            it = __dadd_rn(it, __dsub_rn(1.0, nu));
+        }
+        const double mult = __dmul_rn(__ddiv_rn(it, (double)p.iterations), p.exposure);
+        return color_multiply(p.primary, mult);
+    }
+    if (p.inside) return color_multiply(p.secondary, dist);
+    return 0u;
+}
+
+__global__ void __launch_bounds__(kShadeThreads)
+frb_shade_kernel(const __grid_constant__ RenderParams p)
+{
+    __shared__ __align__(16) uint32_t stage[kShadeThreads * 3];  // 12 B per thread for RGB24
+    const uint64_t npix = (uint64_t)p.rows * p.width;
+    const uint64_t cta_px = (uint64_t)kShadeThreads * kShadePxPerThread;
+    const uint64_t nblocks = (npix + cta_px - 1) / cta_px;
+    for (uint64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+        const uint64_t base = blk * cta_px + (uint64_t)threadIdx.x * kShadePxPerThread;
+        uint32_t c[4] = {0u, 0u, 0u, 0u};
+        if (base + 4 <= npix) {
+            const uint4 n4 = *reinterpret_cast<const uint4 *>(p.iters + base);
+            const uint32_t n[4] = {n4.x, n4.y, n4.z, n4.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) c[k] = shade_pixel(p, n[k], p.zfinal[base + k]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (base + k < npix) c[k] = shade_pixel(p, p.iters[base + k], p.zfinal[base + k]);
+        }
+        const bool full_cta = (blk + 1) * cta_px <= npix;
+        if (p.format == 4u) {
+            if (base + 4 <= npix) {
+                uint4 v = make_uint4(c[0] | 0xff000000u, c[1] | 0xff000000u, c[2] | 0xff000000u, c[3] | 0xff000000u);
+                *reinterpret_cast<uint4 *>(p.out + base * 4) = v;
+            } else {
+                for (int k = 0; k < 4; ++k)
+                    if (base + k < npix) reinterpret_cast<uint32_t *>(p.out)[base + k] = c[k] | 0xff000000u;
+            }
+        } else {
+            // pack 4 px (12 B) as three words: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
+            const uint32_t w0 = c[0] | (c[1] << 24);
+            const uint32_t w1 = (c[1] >> 8) | (c[2] << 16);
+            const uint32_t w2 = (c[2] >> 16) | (c[3] << 8);
+            if (full_cta) {
+                stage[threadIdx.x * 3 + 0] = w0;
+                stage[threadIdx.x * 3 + 1] = w1;
+                stage[threadIdx.x * 3 + 2] = w2;
+                __syncthreads();
+                // 256 threads x 12 B = 3072 B = 192 x 16 B
+                uint4 *dst = reinterpret_cast<uint4 *>(p.out + blk * cta_px * 3);
+                if (threadIdx.x < (kShadeThreads * 3) / 4) dst[threadIdx.x] = reinterpret_cast<const uint4 *>(stage)[threadIdx.x];
+                __syncthreads();
+            } else {
+                uint8_t *dst = p.out + base * 3;
+                const uint32_t w[3] = {w0, w1, w2};
+                for (int k = 0; k < 12; ++k)
+                    if (base * 3 + k < npix * 3) dst[k] = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
+            }
+        }
+    }
+}
+
+}  // namespace frb

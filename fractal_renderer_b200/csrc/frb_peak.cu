@@ -1,0 +1,142 @@
+// frb_peak.cu — FP64 pipe micro-benchmark: the roofline denominator of this path.
+//
+// MEASURED_PEAKS.json (driver-written) has HBM and bf16 tensor peaks but no FP64 figure, and the escape-time
+// recurrence is bounded by the FP64 pipe.  Each kernel keeps 8 independent dependency chains per
+// thread so that the pipe, not the latency, is what is measured; every SM runs 1024 threads.
+#include "../../include/frb.h"
+
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <string>
+
+namespace {
+
+constexpr int kChains = 8;
+constexpr int kInner = 64;  // unrolled repetitions per loop trip
+
+enum { OP_DFMA = 0, OP_DMUL = 1, OP_DADD = 2, OP_MIX6 = 3 };
+
+template <int OP>
+__global__ void __launch_bounds__(256, 4) fp64_peak_kernel(double *sink, long long *cycles, int trips, double m, double c)
+{
+    double acc[kChains];
+#pragma unroll
+    for (int k = 0; k < kChains; ++k) acc[k] = (double)(threadIdx.x + k) * 1e-3;
+    const long long t0 = clock64();
+    if (OP == OP_MIX6) {
+        // the iteration body of frb_iterate_stream_kernel<6> on 4 independent orbits, no exits:
+        // DADD DMUL DADD DFMA DMUL DMUL per orbit per trip
+        double x[4], y[4], a[4], b[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            x[k] = acc[k];
+            y[k] = acc[k + 4];
+            a[k] = x[k] * x[k];
+            b[k] = y[k] * y[k];
+        }
+        for (int t = 0; t < trips; ++t) {
+#pragma unroll
+            for (int r = 0; r < kInner / 4; ++r) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const double s = __dsub_rn(a[k], b[k]);
+                    const double p = __dmul_rn(x[k], y[k]);
+                    x[k] = __dadd_rn(s, c);
+                    y[k] = __fma_rn(p, 2.0, m);
+                    a[k] = __dmul_rn(x[k], x[k]);
+                    b[k] = __dmul_rn(y[k], y[k]);
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            acc[k] = x[k] + a[k];
+            acc[k + 4] = y[k] + b[k];
+        }
+    } else {
+        for (int t = 0; t < trips; ++t) {
+#pragma unroll
+            for (int r = 0; r < kInner; ++r) {
+#pragma unroll
+                for (int k = 0; k < kChains; ++k) {
+                    if (OP == OP_DFMA) acc[k] = __fma_rn(acc[k], m, c);
+                    if (OP == OP_DMUL) acc[k] = __dmul_rn(acc[k], m);
+                    if (OP == OP_DADD) acc[k] = __dadd_rn(acc[k], c);
+                }
+            }
+        }
+    }
+    const long long t1 = clock64();
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < kChains; ++k) s += acc[k];
+    if (s == 123.456) sink[0] = s;  // keep the chains alive without a store in the common case
+    if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
+}
+
+template <int OP>
+cudaError_t run_one(int blocks, int trips, double *sink, long long *cycles, double *instr_per_s, double *mhz)
+{
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    fp64_peak_kernel<OP><<<blocks, 256>>>(sink, cycles, trips / 8, 1.0000001, 1e-9);  // warm-up
+    double best = 0.0, best_mhz = 0.0;
+    for (int rep = 0; rep < 3; ++rep) {
+        cudaEventRecord(e0);
+        fp64_peak_kernel<OP><<<blocks, 256>>>(sink, cycles, trips, 1.0000001, 1e-9);
+        cudaEventRecord(e1);
+        cudaError_t e = cudaEventSynchronize(e1);
+        if (e != cudaSuccess) return e;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double per_thread = (OP == OP_MIX6) ? (double)trips * (kInner / 4) * 4 * 6 : (double)trips * kInner * kChains;
+        const double total = per_thread * 256.0 * blocks;
+        const double rate = total / (ms * 1e-3);
+        long long cyc = 0;
+        cudaMemcpy(&cyc, cycles, sizeof cyc, cudaMemcpyDeviceToHost);
+        if (rate > best) {
+            best = rate;
+            best_mhz = (double)cyc / (ms * 1e-3) / 1e6;
+        }
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *instr_per_s = best;
+    *mhz = best_mhz;
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+extern "C" int frb_measure_fp64_peak(int device, FrbFp64Peak *peak)
+{
+    if (!peak) return FRB_ERR_INVALID;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return FRB_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= n) return FRB_ERR_INVALID;
+    if (cudaSetDevice(device) != cudaSuccess) return FRB_ERR_CUDA;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return FRB_ERR_CUDA;
+    const int blocks = prop.multiProcessorCount * 4;
+    double *sink = nullptr;
+    long long *cycles = nullptr;
+    if (cudaMalloc(&sink, 64) != cudaSuccess) return FRB_ERR_CUDA;
+    if (cudaMalloc(&cycles, sizeof(long long) * blocks) != cudaSuccess) return FRB_ERR_CUDA;
+    const int trips = 4096;  // 4096 * 64 * 8 = 2.1 M FP64 instructions per thread: ~35 ms at nominal peak
+    double mhz[4] = {0, 0, 0, 0};
+    cudaError_t e = run_one<OP_DFMA>(blocks, trips, sink, cycles, &peak->dfma_per_s, &mhz[0]);
+    if (e == cudaSuccess) e = run_one<OP_DMUL>(blocks, trips, sink, cycles, &peak->dmul_per_s, &mhz[1]);
+    if (e == cudaSuccess) e = run_one<OP_DADD>(blocks, trips, sink, cycles, &peak->dadd_per_s, &mhz[2]);
+    if (e == cudaSuccess) e = run_one<OP_MIX6>(blocks, trips, sink, cycles, &peak->mixed6_per_s, &mhz[3]);
+    cudaFree(sink);
+    cudaFree(cycles);
+    peak->sm_clock_mhz = mhz[0];
+    peak->sm_count = (uint32_t)prop.multiProcessorCount;
+    peak->reserved = 0;
+    return e == cudaSuccess ? FRB_OK : FRB_ERR_CUDA;
+}

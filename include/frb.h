@@ -1,0 +1,208 @@
+/*
+ * frb.h — C ABI of the B200-native escape-time renderer ("frb" = fractal renderer, B200).
+ *
+ * This is the drop-in boundary for ONE path of Icelk/fractal-renderer: the Mandelbrot | Julia arm of
+ *     pub fn get_image(config: &Config) -> Vec<RGB>            (reference src/lib.rs:253-270)
+ * i.e. calc::get_recursive_pixel (calc/src/lib.rs:199-235) evaluated for every pixel, row-major.
+ * Everything behind these symbols runs as hand-written sm_100a CUDA; there is NO CPU fallback: every
+ * compute entry point returns FRB_ERR_NO_DEVICE when no CUDA device is usable.
+ *
+ * Conventions
+ *   - plain C types only; the caller owns every host buffer; the library owns device memory, pinned staging
+ *     and streams (created lazily or by frb_init, released by frb_shutdown);
+ *   - every function returns 0 (FRB_OK) or a negative FRB_ERR_* code, never unwinds; the message for the last
+ *     failure on the calling thread is frb_last_error();
+ *   - calls are blocking unless the name ends in _async; the library is thread-safe (concurrent renders from
+ *     several host threads are serialised per device — reference callers src/gui.rs:60 and :325 may overlap);
+ *   - images are row-major, y outer, no row padding; RGB24 = 3 bytes r,g,b per pixel (the memory image of the
+ *     reference's Vec<RGB>, src/lib.rs:13-15), RGBA32 = r,g,b,255 (what src/gui.rs:66-75 builds for egui).
+ */
+#ifndef FRB_H_
+#define FRB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FRB_ABI_VERSION 1u
+
+/* ---- value types: field-for-field mirrors of the reference's calc crate --------------------------------- */
+
+/* calc::Imaginary (calc/src/lib.rs:77-81) */
+typedef struct FrbImaginary {
+    double re;
+    double im;
+} FrbImaginary;
+
+/* calc::RGB (calc/src/lib.rs:119-125): the three STORED fields in declaration order r,g,b.
+ * NB the reference constructor is RGB::new(r, b, g) (calc/src/lib.rs:129-131): callers that mirror
+ * `RGB::new(40, 40, 255)` must store r=40, g=255, b=40. frb_rgb_new() below does that. */
+typedef struct FrbRGB {
+    uint8_t r;
+    uint8_t g;
+    uint8_t b;
+} FrbRGB;
+
+/* calc::Algo (calc/src/lib.rs:150-154), declaration order. */
+enum {
+    FRB_ALGO_MANDELBROT = 0,
+    FRB_ALGO_BARNSLEY_FERN = 1, /* not on this path: rendered as all-black, as get_recursive_pixel does (:211) */
+    FRB_ALGO_JULIA = 2
+};
+
+/* calc::Config (calc/src/lib.rs:21-37), same field order; bools as bytes. 104 bytes, 8-aligned. */
+typedef struct FrbConfig {
+    uint32_t algo;        /* FRB_ALGO_* */
+    uint32_t width;
+    uint32_t height;
+    uint32_t iterations;
+    double limit;         /* escape radius (un-squared) */
+    double stable_limit;  /* compared with the SQUARED distance of the final z (calc/src/lib.rs:216, sic) */
+    FrbImaginary pos;
+    FrbImaginary scale;
+    double exposure;
+    uint8_t inside;
+    uint8_t smooth;
+    FrbRGB primary_color;
+    FrbRGB secondary_color;
+    double color_weight;  /* fern only; carried for layout fidelity, unused */
+    FrbImaginary julia_set;
+} FrbConfig;
+
+/* Fills *cfg with calc::Config::new(algo) (calc/src/lib.rs:39-69). Host-only, needs no device. */
+void frb_config_default(FrbConfig *cfg, uint32_t algo);
+/* RGB::new(r, b, g) with the reference's argument order (calc/src/lib.rs:129-131). Host-only. */
+FrbRGB frb_rgb_new(uint8_t r, uint8_t b, uint8_t g);
+
+/* ---- pixel formats / errors -------------------------------------------------------------------------------- */
+
+enum { FRB_RGB24 = 3, FRB_RGBA32 = 4 }; /* value = bytes per pixel */
+
+enum {
+    FRB_OK = 0,
+    FRB_ERR_NO_DEVICE = -1,   /* no usable CUDA device / driver: there is no CPU path */
+    FRB_ERR_INVALID = -2,     /* bad argument (null pointer, short buffer, unknown format, bad shard) */
+    FRB_ERR_CUDA = -3,        /* a CUDA runtime call failed; see frb_last_error() */
+    FRB_ERR_TOO_LARGE = -4    /* a single launch would exceed 2^32-1 pixels per shard */
+};
+
+/* ---- shards (multi-GPU partition of one frame) ---------------------------------------------- */
+
+/* Interleaved row bands: band k covers image rows [k*band_rows, (k+1)*band_rows); shard `index` of `count`
+ * owns the bands with k % count == index. count=1,index=0,band_rows=0 means the whole frame.
+ * A shard's output is COMPACT: its rows in increasing y, no gaps (frb_shard_rows() of them). */
+typedef struct FrbShard {
+    uint32_t index;
+    uint32_t count;
+    uint32_t band_rows; /* 0 = whole frame as one band */
+    uint32_t reserved;
+} FrbShard;
+
+/* Number of image rows shard owns for an image of `height` rows. Host-only. */
+uint32_t frb_shard_rows(uint32_t height, const FrbShard *shard);
+/* Image row of the shard's local row `local_row` (image of `height` rows). Host-only. */
+uint32_t frb_shard_row_to_y(uint32_t height, const FrbShard *shard, uint32_t local_row);
+
+/* ---- statistics of the last render issued by the calling thread --------------------------------------- */
+
+typedef struct FrbStats {
+    uint64_t pixels;          /* pixels rendered */
+    uint64_t iterations;      /* loop-body executions of calc::recursive summed over pixels (i+1 | iterations) */
+    uint64_t lane_iterations; /* 32 x warp-level loop trips issued by the iterate kernel (lane utilisation = iterations / lane_iterations) */
+    float iterate_ms;         /* device time of the iterate kernel(s), CUDA events */
+    float shade_ms;           /* device time of the shade kernel(s) */
+    float device_ms;          /* first kernel start -> last kernel end on the device */
+    float total_ms;           /* host wall time of the call (includes copies for host-buffer entry points) */
+    uint32_t kernel_launches; /* kernels launched by this render */
+    uint32_t devices;         /* devices that took part */
+    uint32_t kernel_variant;  /* FRB_KERNEL_* actually used for the iteration */
+    uint32_t reserved;
+} FrbStats;
+
+enum {
+    FRB_KERNEL_AUTO = 0,      /* STREAM6 when it is provably bit-exact for the config (always, for sane inputs), else STREAM7 */
+    FRB_KERNEL_STREAM6 = 1,   /* persistent lane-refill kernel, 6 FP64 instructions / iteration (2xy+c.im as one fma) */
+    FRB_KERNEL_STREAM7 = 2,   /* persistent lane-refill kernel, 7 FP64 instructions / iteration, exact for ANY input */
+    FRB_KERNEL_SIMPLE = 3     /* one thread per pixel, reference operation order as written (11 FP64 instructions), no
+                                 queue: the on-GPU cross-check for the two above */
+};
+
+/* ---- lifecycle ------------------------------------------------------------------------------------------ */
+
+/* Number of usable CUDA devices (0 if none; never fails). */
+int frb_device_count(void);
+/* Optional eager initialisation. device_mask bit d = use device d; 0 = all visible devices.
+ * Creates contexts, streams and work queues so that the first render is not charged for them. */
+int frb_init(uint32_t device_mask);
+/* Releases all device and pinned memory, streams and events. Safe to call repeatedly. */
+void frb_shutdown(void);
+/* Forces the iteration kernel (FRB_KERNEL_*) for subsequent renders of this thread; FRB_KERNEL_AUTO restores
+ * the default. Test/bench hook. */
+int frb_set_kernel_variant(uint32_t variant);
+
+/* ---- render: host-buffer entry points (what the reference's get_image binds to) ---------------------- */
+
+/* Renders the whole frame on device `device` (-1 = spread over all initialised devices by interleaved
+ * 16-row bands) and writes width*height*format bytes into the HOST buffer `out` (out_len >= that).
+ * Replaces get_image's Mandelbrot|Julia arm (src/lib.rs:255-269). */
+int frb_render(const FrbConfig *cfg, uint8_t *out, size_t out_len, uint32_t format, int device);
+
+/* Renders one shard of the frame on `device` into a HOST buffer, compact layout (see FrbShard). */
+int frb_render_shard(const FrbConfig *cfg, const FrbShard *shard, uint8_t *out, size_t out_len,
+                     uint32_t format, int device);
+
+/* Parity hook: the raw result of calc::recursive (calc/src/lib.rs:245-257) per pixel of the shard
+ * (shard may be NULL = whole frame): iters[p] = returned count (index of the escaping iteration, or
+ * `iterations`), zfinal[2p],zfinal[2p+1] = returned position. HOST buffers; zfinal may be NULL. */
+int frb_render_counts(const FrbConfig *cfg, const FrbShard *shard, uint32_t *iters, double *zfinal,
+                      int device);
+
+/* n independent frames (zoom animation); frame k goes to device k % devices (device = -1) or
+ * all to `device`; out holds the frames back to back, each width_k*height_k*format bytes. */
+int frb_render_frames(const FrbConfig *cfgs, uint32_t n, uint8_t *out, size_t out_len, uint32_t format,
+                      int device);
+
+/* ---- render: device-buffer entry points (no host copies; bench `value`, GPU-resident consumers) ----- */
+
+/* Same as frb_render_shard but `dev_out` is DEVICE memory on `device` (>= rows*width*format bytes,
+ * 16-byte aligned). `stream` is a cudaStream_t (NULL = the library's own stream for that device).
+ * Returns after enqueueing; results are complete when `stream` has drained. Stats (iterations etc.)
+ * are harvested by frb_sync_stats(). */
+int frb_render_device_async(const FrbConfig *cfg, const FrbShard *shard, void *dev_out, size_t out_len,
+                            uint32_t format, int device, void *stream);
+/* Waits for the last *_async render of this thread and fills its statistics. */
+int frb_sync_stats(FrbStats *stats);
+/* Same for the *_async render issued `back` calls before the last one by this thread (0 = the last; the
+ * library keeps the 32 most recent), so a caller can keep the next frame enqueued while harvesting. */
+int frb_async_stats(uint32_t back, FrbStats *stats);
+
+/* ---- diagnostics ---------------------------------------------------------------------------------------- */
+
+/* Message for the last error on this thread ("" if none). Valid until the next failing call on this thread. */
+const char *frb_last_error(void);
+/* Statistics of the last blocking render on this thread. */
+int frb_last_stats(FrbStats *stats);
+/* ABI version of the loaded library (== FRB_ABI_VERSION). */
+uint32_t frb_abi_version(void);
+
+/* Measures the FP64 pipe of `device`: dependent-chain-free DFMA / DMUL / DADD streams on every SM.
+ * Results in instructions per second (thread-level, i.e. lanes x warp-instructions). This is the
+ * roofline denominator for this path (MEASURED_PEAKS.json has no FP64 entry). */
+typedef struct FrbFp64Peak {
+    double dfma_per_s;
+    double dmul_per_s;
+    double dadd_per_s;
+    double mixed6_per_s;  /* the 6-instruction iteration body as an independent stream (no exits) */
+    double sm_clock_mhz;  /* average SM clock observed during the run (clock64 / event time) */
+    uint32_t sm_count;
+    uint32_t reserved;
+} FrbFp64Peak;
+int frb_measure_fp64_peak(int device, FrbFp64Peak *peak);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FRB_H_ */

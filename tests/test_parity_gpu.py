@@ -1,0 +1,205 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle.  Run on a B200: `pytest -m gpu`.
+
+Bar: escape counts and final-z bits BIT-EXACT; 8-bit colour channels within +-1 LSB (only log2,
+which the reference takes from the platform libm, can differ).  NaN final positions compare as a class (x86 and
+CUDA produce different NaN sign/payload bits; the reference defines neither)."""
+import os
+import threading
+
+import numpy as np
+import pytest
+
+import cases
+import oracle_binding as ob
+from fractal_renderer_b200 import configs
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+COLOUR_TOL = 1  # LSB, stated by BASELINE.json north_star
+
+
+def z_equal(a: np.ndarray, b: np.ndarray) -> np.ndarray:
+    """bitwise equality, NaN == NaN as a class"""
+    same = a.view(np.uint64) == b.view(np.uint64)
+    return same | (np.isnan(a) & np.isnan(b))
+
+
+def assert_parity(frb, cfg, ref, shard=None, variant=None, what=""):
+    frb.set_kernel_variant(variant if variant is not None else frb.KERNEL_AUTO)
+    try:
+        iters, z = frb.render_counts(cfg, shard=shard)
+        stats = frb.last_stats()
+        sh = shard if shard is not None else frb.Shard()
+        rgb = frb.render_shard(cfg, sh, frb.FRB_RGB24)
+        rgba = frb.render_shard(cfg, sh, frb.FRB_RGBA32)
+    finally:
+        frb.set_kernel_variant(frb.KERNEL_AUTO)
+    assert np.array_equal(iters, ref["iters"]), f"{what}: {np.count_nonzero(iters != ref['iters'])} escape counts differ"
+    zq = z_equal(z, ref["z"])
+    assert zq.all(), f"{what}: {np.count_nonzero(~zq)} final-z components differ in bits"
+    d = np.abs(rgb.astype(np.int16) - ref["rgb"].astype(np.int16))
+    assert d.max(initial=0) <= COLOUR_TOL, f"{what}: colour off by {d.max()} LSB"
+    assert np.array_equal(rgba[..., :3], rgb) and (rgba[..., 3] == 255).all(), f"{what}: RGBA32 != RGB24 + alpha"
+    if cfg.algo != 1:
+        assert stats["iterations"] == ref["total"], f"{what}: iteration total {stats['iterations']} != {ref['total']}"
+    return int(np.count_nonzero(d)), stats
+
+
+SMALL = cases.all_small_cases()
+
+
+@pytest.mark.parametrize("name", sorted(SMALL))
+def test_small_cases_vs_oracle_and_golden(gpu, name):
+    cfg = SMALL[name]
+    ref = ob.render_rows(cfg, threads=1)
+    g = np.load(os.path.join(GOLDEN, "small_cases.npz"))
+    assert np.array_equal(ref["iters"], g[name + "/iters"])  # the live oracle is the frozen oracle
+    golden = dict(iters=g[name + "/iters"], z=g[name + "/zbits"].view(np.float64), rgb=g[name + "/rgb"], total=int(g[name + "/total"]))
+    assert_parity(gpu, cfg, golden, what=name + "/auto")
+
+
+@pytest.mark.parametrize("variant", ["stream6", "stream7", "simple"])
+@pytest.mark.parametrize("name", ["mandel_default", "mandel_iter0", "mandel_iter9", "mandel_limit1p5", "mandel_limit1e155",
+                                  "mandel_limit_nan", "mandel_real_axis", "mandel_deep_subulp", "julia_default",
+                                  "julia_c3_view", "C1_small", "C2_small", "C4_small"])
+def test_every_kernel_variant(gpu, name, variant):
+    """Forcing each kernel: STREAM7 and SIMPLE are exact for any input; STREAM6 is exact for these (sane) inputs."""
+    cfg = SMALL[name]
+    if variant == "stream6" and name in ("mandel_limit1e155", "mandel_limit_nan"):
+        pytest.skip("outside FORM 6's proven domain; AUTO routes these to STREAM7")
+    v = {"stream6": gpu.KERNEL_STREAM6, "stream7": gpu.KERNEL_STREAM7, "simple": gpu.KERNEL_SIMPLE}[variant]
+    ref = ob.render_rows(cfg, threads=1)
+    _, stats = assert_parity(gpu, cfg, ref, variant=v, what=f"{name}/{variant}")
+    assert stats["kernel_variant"] == v
+
+
+def test_auto_routes_exotic_inputs_to_form7(gpu):
+    for name, expect in [("mandel_default", gpu.KERNEL_STREAM6), ("julia_default", gpu.KERNEL_STREAM6),
+                         ("julia_zero", gpu.KERNEL_STREAM7), ("julia_real_c", gpu.KERNEL_STREAM7),
+                         ("julia_tiny_im", gpu.KERNEL_STREAM7), ("mandel_limit1e155", gpu.KERNEL_STREAM7),
+                         ("mandel_limit_nan", gpu.KERNEL_STREAM7), ("mandel_huge_coords", gpu.KERNEL_STREAM7),
+                         ("mandel_real_axis", gpu.KERNEL_STREAM6)]:
+        gpu.render_counts(SMALL[name])
+        assert gpu.last_stats()["kernel_variant"] == expect, name
+
+
+def test_c1_full_frame(gpu):
+    """C1 = the config that 'runs on the reference CPU path': every pixel of the 1920x1080 frame."""
+    cfg = configs.c1()
+    ref = ob.render_rows(cfg)
+    assert ref["total"] == configs.TOTAL_ITERATIONS["C1"]
+    ndiff, _ = assert_parity(gpu, cfg, ref, what="C1")
+    assert ndiff <= cfg.width * cfg.height // 10000  # colours are expected identical; allow log2 ulp ties
+
+
+def test_c3_full_frame(gpu):
+    cfg = configs.c3()
+    ref = ob.render_rows(cfg)
+    assert ref["total"] == configs.TOTAL_ITERATIONS["C3"]
+    assert_parity(gpu, cfg, ref, what="C3")
+
+
+def test_c2_full_frame(gpu):
+    """The north-star frame, all 9 M pixels (the oracle needs a few seconds on the box's cores)."""
+    cfg = configs.c2()
+    ref = ob.render_rows(cfg)
+    assert ref["total"] == configs.TOTAL_ITERATIONS["C2"]
+    assert_parity(gpu, cfg, ref, what="C2")
+
+
+def test_c4_shards_vs_oracle(gpu):
+    """C4 is 268 Mpx / 5.7e11 iterations: check three of 128 interleaved-band shards (128 rows each) bit for bit —
+    the same partition the 8-GPU run uses (16-row bands)."""
+    cfg = configs.c4()
+    for idx in (0, 77, 127):
+        sh = gpu.Shard(idx, 128, 16)
+        rows = sh.image_rows(cfg.height)
+        assert len(rows) == 128
+        ref = ob.render_rows(cfg, rows=rows)
+        assert_parity(gpu, cfg, ref, shard=sh, what=f"C4 shard {idx}/128")
+
+
+def test_c5_frames(gpu):
+    """Three frames of the zoom through frb_render_frames (the animation entry point), against the oracle."""
+    ks = [0, 100, 239]
+    cfgs = [configs.c5_frame(k).with_(width=480, height=270) for k in ks]
+    out = gpu.render_frames(cfgs, gpu.FRB_RGB24, device=0)
+    total = 0
+    off = 0
+    for cfg in cfgs:
+        ref = ob.render_rows(cfg)
+        n = cfg.width * cfg.height * 3
+        got = out[off:off + n].reshape(cfg.height, cfg.width, 3)
+        off += n
+        assert np.abs(got.astype(int) - ref["rgb"].astype(int)).max() <= COLOUR_TOL
+        total += ref["total"]
+    assert gpu.last_stats()["iterations"] == total
+
+
+def test_full_size_properties_c2_variants_agree(gpu):
+    """At full size, the three kernels must agree with each other bit for bit (SIMPLE is the reference order as
+    written, on the GPU) and hit the exact iteration total."""
+    cfg = configs.c2()
+    res = {}
+    for v in (gpu.KERNEL_STREAM6, gpu.KERNEL_STREAM7, gpu.KERNEL_SIMPLE):
+        gpu.set_kernel_variant(v)
+        try:
+            res[v] = gpu.render_counts(cfg)
+            assert gpu.last_stats()["iterations"] == configs.TOTAL_ITERATIONS["C2"]
+        finally:
+            gpu.set_kernel_variant(gpu.KERNEL_AUTO)
+    base = res[gpu.KERNEL_SIMPLE]
+    for v in (gpu.KERNEL_STREAM6, gpu.KERNEL_STREAM7):
+        assert np.array_equal(res[v][0], base[0])
+        assert z_equal(res[v][1], base[1]).all()
+
+
+def test_shards_tile_the_frame(gpu):
+    cfg = configs.c1().with_(width=333, height=250)
+    full = gpu.get_image(cfg).reshape(cfg.height, cfg.width, 3)
+    for count, br in [(2, 16), (3, 7), (8, 16), (8, 1)]:
+        img = np.zeros_like(full)
+        for i in range(count):
+            sh = gpu.Shard(i, count, br)
+            img[sh.image_rows(cfg.height)] = gpu.render_shard(cfg, sh)
+        assert np.array_equal(img, full), (count, br)
+
+
+def test_render_all_devices_matches_single(gpu):
+    cfg = configs.c1().with_(width=640, height=403)
+    one = gpu.get_image(cfg, device=0)
+    allv = gpu.get_image(cfg, device=-1)
+    assert np.array_equal(one, allv)
+
+
+def test_idempotent_and_reentrant(gpu):
+    """Two host threads rendering at once (the GUI's render thread and its screenshot thread may overlap:
+    src/gui.rs:60 and :325) must both get the right frame."""
+    a = configs.c1().with_(width=400, height=300)
+    b = configs.c3().with_(width=256, height=256)
+    ra, rb = gpu.get_image(a), gpu.get_image(b)
+    out = {}
+
+    def work(key, cfg, n):
+        for _ in range(n):
+            out[key] = gpu.get_image(cfg)
+
+    ta = threading.Thread(target=work, args=("a", a, 6))
+    tb = threading.Thread(target=work, args=("b", b, 6))
+    ta.start(); tb.start(); ta.join(); tb.join()
+    assert np.array_equal(out["a"], ra) and np.array_equal(out["b"], rb)
+
+
+def test_invalid_arguments(gpu):
+    cfg = configs.c1().with_(width=16, height=16)
+    small = np.empty(10, np.uint8)
+    with pytest.raises(gpu.FrbError) as e:
+        gpu.get_image_into(cfg, small)
+    assert e.value.code == -2
+    with pytest.raises(gpu.FrbError):
+        gpu.render_shard(cfg, gpu.Shard(3, 2, 16))
+    with pytest.raises(gpu.FrbError):
+        gpu.get_image(cfg, device=99)
+    empty = gpu.get_image(cfg.with_(width=0))
+    assert empty.size == 0
