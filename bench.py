@@ -49,7 +49,7 @@ def parse():
     ap.add_argument("--workload", default="C2", choices=["C1", "C2", "C2b", "C3", "C4"])
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--kernel", default="auto", choices=["auto", "stream6", "stream7", "simple"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "stream6", "stream7", "simple", "dense6"])
     return ap.parse_args()
 
 
@@ -219,7 +219,7 @@ def main():
         dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
         dist = dist_mod
     frb.init(1 << local)
-    variant = {"auto": frb.KERNEL_AUTO, "stream6": frb.KERNEL_STREAM6, "stream7": frb.KERNEL_STREAM7, "simple": frb.KERNEL_SIMPLE}[args.kernel]
+    variant = {"auto": frb.KERNEL_AUTO, "stream6": frb.KERNEL_STREAM6, "stream7": frb.KERNEL_STREAM7, "simple": frb.KERNEL_SIMPLE, "dense6": frb.KERNEL_DENSE6}[args.kernel]
     frb.set_kernel_variant(variant)
 
     shard = frb.Shard(rank, world, 16) if (world > 1 and args.scaling == "strong") else frb.Shard()
@@ -251,7 +251,9 @@ def main():
     # FP64 peak of this GPU, measured now (rank-local; ~0.3 s)
     peak = frb.measure_fp64_peak(local)
 
-    stream = torch.cuda.current_stream()
+    # a real (non-default) stream: the library launches on it and the CUDA events below are recorded on it
+    stream = torch.cuda.Stream(device=local)
+    assert stream.cuda_stream != 0
     c_cfg, c_shard = cfg.to_c(), shard.to_c()
 
     def step_device():
@@ -325,12 +327,14 @@ def main():
     per_launch_iters = my_iters / args.steps
     achieved_tflops = per_launch_iters * FLOP_PER_ITER / (it_ms * 1e-3) / 1e12
     peak_tflops = peak["dfma_per_s"] * 2 / 1e12
-    form = 6 if kernel_variant == frb.KERNEL_STREAM6 else (7 if kernel_variant == frb.KERNEL_STREAM7 else 11)
+    form = {frb.KERNEL_STREAM6: 6, frb.KERNEL_DENSE6: 6, frb.KERNEL_STREAM7: 7}.get(kernel_variant, 11)
+    kname = {frb.KERNEL_STREAM6: "frb_iterate_sparse_kernel<6>", frb.KERNEL_DENSE6: "frb_iterate_stream_kernel<6>",
+             frb.KERNEL_STREAM7: "frb_iterate_stream_kernel<7>"}.get(kernel_variant, "frb_iterate_simple_kernel")
     roofline = {
         "bound": "fp64",
         "achieved": round(achieved_tflops, 3), "peak": round(peak_tflops, 3), "unit": "TFLOP/s",
         "frac": round(achieved_tflops / peak_tflops, 4), "traffic": None,
-        "kernel": f"frb_iterate_stream_kernel<{form}>" if form != 11 else "frb_iterate_simple_kernel",
+        "kernel": kname,
         "kernel_ms": round(it_ms, 4), "shade_kernel_ms": round(statistics.mean(shade_ms), 4),
         "kernel_share_of_step": round(it_ms * args.steps / dev_ms, 4) if world == 1 else None,
         "peak_source": "measured in this run: frb_measure_fp64_peak DFMA stream x 2 flop (MEASURED_PEAKS.json has no FP64 entry)",

@@ -69,7 +69,7 @@ struct DeviceCtx {
     int dev = -1;
     bool ready = false;
     int sm_count = 0;
-    int iter_blocks_per_sm[2] = {0, 0};  // FORM 6, FORM 7
+    int iter_blocks_per_sm[3] = {0, 0, 0};  // dense FORM 6, dense FORM 7, sparse FORM 6
     cudaStream_t stream = nullptr;       // the library's own stream for this device
     cudaEvent_t ev_guard = nullptr;      // completion of the last render that used the shared raw buffers
     cudaStream_t last_stream = nullptr;
@@ -134,7 +134,9 @@ int ctx_init(DeviceCtx *c, int dev)
                                                      frb::kIterateThreads, 0));
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->iter_blocks_per_sm[1], frb::frb_iterate_stream_kernel<7>,
                                                      frb::kIterateThreads, 0));
-    if (c->iter_blocks_per_sm[0] < 1 || c->iter_blocks_per_sm[1] < 1)
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->iter_blocks_per_sm[2], frb::frb_iterate_sparse_kernel<6>,
+                                                     frb::kIterateThreads, 0));
+    if (c->iter_blocks_per_sm[0] < 1 || c->iter_blocks_per_sm[1] < 1 || c->iter_blocks_per_sm[2] < 1)
         return fail(FRB_ERR_CUDA, "iterate kernel does not fit on device %d", dev);
     c->ready = true;
     return FRB_OK;
@@ -291,6 +293,28 @@ bool form6_is_exact(const FrbConfig &cfg)
     return true;
 }
 
+// The sparse-check kernel tests for escape once per block of kSparseU iterations; that is only sound when an
+// escaped orbit provably keeps growing (see frb_kernels.cuh): R = |limit| >= 4 and |c| <= R^2 - 3R for every pixel.
+bool sparse_is_safe(const FrbConfig &cfg)
+{
+    if (!form6_is_exact(cfg)) return false;
+    if (cfg.iterations < 4u * (uint32_t)frb::kSparseU) return false;  // too short to amortise a block
+    const double R = std::fabs(cfg.limit);
+    if (!(R >= 4.0) || !(R <= 1e150)) return false;
+    double cmax;
+    if (cfg.algo == FRB_ALGO_JULIA) {
+        cmax = std::hypot(cfg.julia_set.re, cfg.julia_set.im);
+    } else {
+        const double wf = (double)cfg.width, hf = (double)cfg.height;
+        const double re_a = host_coord(0.0, hf, (wf / hf) / 2.0, cfg.pos.re, cfg.scale.re);
+        const double re_b = host_coord((double)(cfg.width ? cfg.width - 1 : 0), hf, (wf / hf) / 2.0, cfg.pos.re, cfg.scale.re);
+        const double im_a = host_coord(0.0, hf, 0.5, cfg.pos.im, cfg.scale.im);
+        const double im_b = host_coord((double)(cfg.height ? cfg.height - 1 : 0), hf, 0.5, cfg.pos.im, cfg.scale.im);
+        cmax = std::hypot(std::max(std::fabs(re_a), std::fabs(re_b)), std::max(std::fabs(im_a), std::fabs(im_b)));
+    }
+    return cmax * 1.0000001 <= R * R - 3.0 * R;
+}
+
 struct Plan {
     RenderParams p;
     uint32_t variant;
@@ -343,7 +367,7 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     plan->npix = npix;
     plan->out_bytes = (size_t)npix * format;
     uint32_t v = tl_variant;
-    if (v == FRB_KERNEL_AUTO) v = form6_is_exact(cfg) ? FRB_KERNEL_STREAM6 : FRB_KERNEL_STREAM7;
+    if (v == FRB_KERNEL_AUTO) v = sparse_is_safe(cfg) ? FRB_KERNEL_STREAM6 : (form6_is_exact(cfg) ? FRB_KERNEL_DENSE6 : FRB_KERNEL_STREAM7);
     plan->variant = v;
 
     if (int rc = ensure(c.tab, c.tab_cap, (size_t)cfg.width + cfg.height + 2)) return rc;
@@ -386,15 +410,17 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
                 dim3 grid(p.rows, (p.width + 255) / 256);
                 frb::frb_iterate_simple_kernel<<<grid, 256, 0, st>>>(p);
             } else {
-                const int form_idx = (plan.variant == FRB_KERNEL_STREAM7) ? 1 : 0;
+                const int kidx = (plan.variant == FRB_KERNEL_STREAM7) ? 1 : (plan.variant == FRB_KERNEL_DENSE6 ? 0 : 2);
                 const uint32_t warps_per_block = frb::kIterateThreads / 32;
-                uint32_t blocks = (uint32_t)(c.sm_count * c.iter_blocks_per_sm[form_idx]);
+                uint32_t blocks = (uint32_t)(c.sm_count * c.iter_blocks_per_sm[kidx]);
                 const uint32_t needed = (p.total_chunks + warps_per_block - 1) / warps_per_block;
                 blocks = std::max(1u, std::min(blocks, needed));
-                if (form_idx == 0)
+                if (kidx == 0)
                     frb::frb_iterate_stream_kernel<6><<<blocks, frb::kIterateThreads, 0, st>>>(p);
-                else
+                else if (kidx == 1)
                     frb::frb_iterate_stream_kernel<7><<<blocks, frb::kIterateThreads, 0, st>>>(p);
+                else
+                    frb::frb_iterate_sparse_kernel<6><<<blocks, frb::kIterateThreads, 0, st>>>(p);
             }
             slot.launches++;
         } else {
@@ -594,7 +620,7 @@ void frb_shutdown(void)
 
 int frb_set_kernel_variant(uint32_t variant)
 {
-    if (variant > FRB_KERNEL_SIMPLE) return fail(FRB_ERR_INVALID, "unknown kernel variant %u", variant);
+    if (variant > FRB_KERNEL_DENSE6) return fail(FRB_ERR_INVALID, "unknown kernel variant %u", variant);
     tl_variant = variant;
     return FRB_OK;
 }

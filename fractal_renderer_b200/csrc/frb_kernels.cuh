@@ -319,6 +319,174 @@ frb_iterate_stream_kernel(const __grid_constant__ RenderParams p)
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// K1b: persistent lane-refill iterate kernel with SPARSE escape checks (the default for sane inputs).
+//
+// Measured on B200 (scripts/issue_probe.cu, profiles/): an FP64 instruction occupies an SMSP's issue port for two
+// cycles and every other instruction for one, so the per-iteration filter of the kernel above (VIMNMX, ISETP, BRA)
+// costs 4 of 16 issue cycles.  This kernel issues NOTHING but the 6 FP64 instructions per iteration inside a block
+// of kSparseU iterations; each step's position is left in its own registers (hx[k], hy[k]: no moves, the unrolled
+// block simply rotates registers) and ONE filter per block tests the last step's squares.
+//
+// Why one test per block suffices (host-checked precondition, frb_api.cu: sparse_is_safe): with R = limit >= 4
+// and |c| <= R^2 - 3R for every pixel, once |z_k|^2 > S = R^2 every later step has |z_m| >= |z_{m-1}|^2 - |c| >= 2R,
+// i.e. max(re^2, im^2) >= 2S, growing doubly exponentially to +inf and then NaN (inf - inf) — all of which pass
+// the unsigned high-word filter.  So "filter fails at the end of the block" proves no step of the block escaped.
+// When it fires, the exact reference test (re^2 + im^2 > S, same products, same sum) is replayed on the recorded
+// positions to find the first escaping step; the reference's count and final position come out bit-identical.
+// A lane whose block-end filter fired without any step escaping (S/2 <= max < S) just carries on.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kSparseU = 8;
+constexpr uint32_t kIdleLeft = 0x80000000u;  // "iterations left" of a lane without a pixel (zero orbit, never attends)
+
+template <int FORM>
+__global__ void __launch_bounds__(kIterateThreads, 3)
+frb_iterate_sparse_kernel(const __grid_constant__ RenderParams p)
+{
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr uint32_t U = (uint32_t)kSparseU;
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+
+    const double S = p.limit_sq;
+    const uint32_t filter_hi = p.filter_hi;
+    const uint32_t iterations = p.iterations;
+    const bool julia = (p.algo == kAlgoJulia);
+
+    Orbit o = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    double hx[kSparseU], hy[kSparseU];
+#pragma unroll
+    for (int k = 0; k < kSparseU; ++k) hx[k] = hy[k] = 0.0;
+    uint32_t left = kIdleLeft;  // iterations still to run for the lane's pixel
+    uint32_t pix = 0;
+    bool active = false;
+    bool cand = false;          // the last block's end-of-block filter fired for this lane
+
+    uint32_t cur_x = 0, cur_end = 0, cur_rowpix = 0;
+    double cur_im = 0.0;
+    bool drained = false;
+    uint32_t next_chunk = 0;
+    if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
+
+    unsigned long long useful = 0;
+    unsigned long long trips = 0;       // lock-step blocks issued by this warp (every lane counts the same)
+    uint32_t left_mark = left;
+
+    for (;;) {
+        // ------------------------------ service (cold) ------------------------------
+        trips += (unsigned long long)((left_mark - left) / U);
+        for (;;) {
+            bool done = false;
+            uint32_t count = iterations;
+            if (active) {
+                if (cand) {
+                    // replay the reference's test on the recorded steps of the last block
+                    const uint32_t i0 = iterations - (left + U);  // index of the block's first iteration
+                    bool found = false;
+#pragma unroll
+                    for (int k = 0; k < kSparseU; ++k) {
+                        if (!found) {
+                            const double xa = __dmul_rn(hx[k], hx[k]);
+                            const double yb = __dmul_rn(hy[k], hy[k]);
+                            const uint32_t m = max((uint32_t)__double2hiint(xa), (uint32_t)__double2hiint(yb));
+                            if (m >= filter_hi && __dadd_rn(xa, yb) > S) {
+                                found = true;
+                                count = i0 + (uint32_t)k;
+                                o.x = hx[k];
+                                o.y = hy[k];
+                            }
+                        }
+                    }
+                    done = found;
+                }
+                if (!done && left < U) {
+                    // fewer than U iterations left: finish with the per-iteration test
+                    done = true;
+                    const uint32_t i0 = iterations - left;
+                    for (uint32_t k = 0; k < left; ++k) {
+                        stream_core<FORM>(o);
+                        if (stream_filter(o, filter_hi) && stream_escaped(o, S)) {
+                            count = i0 + k;
+                            break;
+                        }
+                    }
+                }
+                if (done) {
+                    p.iters[pix] = count;
+                    p.zfinal[pix] = make_double2(o.x, o.y);
+                    useful += (count < iterations) ? (unsigned long long)count + 1ull : (unsigned long long)iterations;
+                    active = false;
+                }
+            }
+            cand = false;
+            if (!active) {
+                // park: zero orbit never fires the filter; kIdleLeft never runs out
+                o.x = o.y = o.a = o.b = o.cr = o.ci = 0.0;
+                left = kIdleLeft;
+            }
+            unsigned need = __ballot_sync(FULL, !active);
+            while (!drained && need != 0u) {
+                if (cur_x == cur_end) {
+                    const uint32_t c = __shfl_sync(FULL, next_chunk, 0);
+                    if (c >= p.total_chunks) {
+                        drained = true;
+                        break;
+                    }
+                    if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
+                    const uint32_t lr = c / p.chunks_per_row;
+                    const uint32_t seg = c - lr * p.chunks_per_row;
+                    cur_x = seg * p.chunk;
+                    cur_end = min(cur_x + p.chunk, p.width);
+                    cur_rowpix = lr * p.width;
+                    cur_im = __ldg(p.tab_im + local_row_to_y(p, lr));
+                }
+                const uint32_t avail = cur_end - cur_x;
+                const uint32_t rank = __popc(need & lt_mask);
+                if (!active && rank < avail) {
+                    const uint32_t px = cur_x + rank;
+                    const double re0 = __ldg(p.tab_re + px);
+                    o.x = re0;
+                    o.y = cur_im;
+                    o.cr = julia ? p.julia_re : re0;
+                    o.ci = julia ? p.julia_im : cur_im;
+                    o.a = __dmul_rn(re0, re0);
+                    o.b = __dmul_rn(cur_im, cur_im);
+                    left = iterations;
+                    pix = cur_rowpix + px;
+                    active = true;
+                }
+                cur_x += min((uint32_t)__popc(need), avail);
+                need = __ballot_sync(FULL, !active);
+            }
+            if (need == FULL) goto finished;                       // drained, nothing in flight
+            if (!__any_sync(FULL, active && left < U)) break;      // everyone can run a full block
+        }
+        left_mark = left;
+
+        // ------------------------------ hot ------------------------------
+        // Per block: kSparseU x 6 FP64 instructions, then IADD, VIMNMX, 2 x ISETP, VOTE, BRA.
+        bool attn;
+        do {
+#pragma unroll
+            for (int k = 0; k < kSparseU; ++k) {
+                stream_core<FORM>(o);
+                hx[k] = o.x;
+                hy[k] = o.y;
+            }
+            left -= U;
+            cand = stream_filter(o, filter_hi);
+            attn = cand || (left < U);
+        } while (!__any_sync(FULL, attn));
+    }
+finished:
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) useful += __shfl_xor_sync(FULL, useful, s);
+    if (lane == 0) {
+        atomicAdd(p.stats + 0, useful);
+        atomicAdd(p.stats + 1, trips * (unsigned long long)(32 * kSparseU));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // K1s: cross-check kernel — one thread per pixel, reference order as written, no queue, no refill.
 // Lock-step warps of 32x1 pixels, so slower than the stream kernels; used to validate the stream kernels at full
 // frame sizes where the CPU oracle would need minutes, and available as FRB_KERNEL_SIMPLE.
@@ -358,10 +526,11 @@ frb_iterate_simple_kernel(const __grid_constant__ RenderParams p)
 // K2: shade.  Raw (count, final z) -> colour, at full lane efficiency, 16-byte coalesced stores.
 // ---------------------------------------------------------------------------------------------------------
 
-// Rust `f64 as u8`: truncate toward zero, saturate, NaN -> 0.  cvt.rzi.u32.f64 saturates and maps NaN to 0.
+// Rust `f64 as u8`: truncate toward zero, saturate to [0, 255], NaN -> 0.  cvt.rzi.u32.f64 saturates negatives to 0
+// and large values to 2^32-1; NaN is handled explicitly (measured on B200: the conversion does not return 0 for it).
 __device__ __forceinline__ uint32_t sat_u8(double v)
 {
-    return min(__double2uint_rz(v), 255u);
+    return (v == v) ? min(__double2uint_rz(v), 255u) : 0u;
 }
 
 // color_multiply (calc/src/lib.rs:133-139): RGB::new(r*m, g*m, b*m) with new(r, b, g) => out.g = b*m, out.b = g*m.

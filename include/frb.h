@@ -123,11 +123,15 @@ typedef struct FrbStats {
 } FrbStats;
 
 enum {
-    FRB_KERNEL_AUTO = 0,      /* STREAM6 when it is provably bit-exact for the config (always, for sane inputs), else STREAM7 */
-    FRB_KERNEL_STREAM6 = 1,   /* persistent lane-refill kernel, 6 FP64 instructions / iteration (2xy+c.im as one fma) */
-    FRB_KERNEL_STREAM7 = 2,   /* persistent lane-refill kernel, 7 FP64 instructions / iteration, exact for ANY input */
-    FRB_KERNEL_SIMPLE = 3     /* one thread per pixel, reference operation order as written (11 FP64 instructions), no
-                                 queue: the on-GPU cross-check for the two above */
+    FRB_KERNEL_AUTO = 0,      /* STREAM6 when its preconditions hold (every sane input), else DENSE6, else STREAM7 */
+    FRB_KERNEL_STREAM6 = 1,   /* persistent lane-refill kernel, 6 FP64 instructions / iteration, one escape filter per
+                                 block of 8 iterations (needs limit >= 4 and |c| <= limit^2 - 3 limit: an escaped orbit
+                                 then provably keeps growing) */
+    FRB_KERNEL_STREAM7 = 2,   /* persistent lane-refill kernel, 7 FP64 instructions / iteration, filter every
+                                 iteration: exact for ANY input */
+    FRB_KERNEL_SIMPLE = 3,    /* one thread per pixel, reference operation order as written (11 FP64 instructions), no
+                                 queue: the on-GPU cross-check for the others */
+    FRB_KERNEL_DENSE6 = 4     /* as STREAM6 but with the filter every iteration (small limits, short iteration caps) */
 };
 
 /* ---- lifecycle ------------------------------------------------------------------------------------------ */
