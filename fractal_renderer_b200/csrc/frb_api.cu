@@ -294,13 +294,13 @@ bool form6_is_exact(const FrbConfig &cfg)
 }
 
 // The sparse-check kernel tests for escape once per block of kSparseU iterations; that is only sound when an
-// escaped orbit provably keeps growing (see frb_kernels.cuh): R = |limit| >= 4 and |c| <= R^2 - 3R for every pixel.
+// escaped orbit provably keeps growing (see frb_kernels.cuh): R = |limit| >= 8 and |c| <= R^2/2 - 3R for every pixel.
 bool sparse_is_safe(const FrbConfig &cfg)
 {
     if (!form6_is_exact(cfg)) return false;
     if (cfg.iterations < 4u * (uint32_t)frb::kSparseU) return false;  // too short to amortise a block
     const double R = std::fabs(cfg.limit);
-    if (!(R >= 4.0) || !(R <= 1e150)) return false;
+    if (!(R >= 8.0) || !(R <= 1e150)) return false;
     double cmax;
     if (cfg.algo == FRB_ALGO_JULIA) {
         cmax = std::hypot(cfg.julia_set.re, cfg.julia_set.im);
@@ -312,7 +312,7 @@ bool sparse_is_safe(const FrbConfig &cfg)
         const double im_b = host_coord((double)(cfg.height ? cfg.height - 1 : 0), hf, 0.5, cfg.pos.im, cfg.scale.im);
         cmax = std::hypot(std::max(std::fabs(re_a), std::fabs(re_b)), std::max(std::fabs(im_a), std::fabs(im_b)));
     }
-    return cmax * 1.0000001 <= R * R - 3.0 * R;
+    return cmax * 1.0000001 <= 0.5 * R * R - 3.0 * R;
 }
 
 struct Plan {
@@ -344,6 +344,10 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
         p.limit_sq = s;
     }
     p.filter_hi = (uint32_t)(double_bits(p.limit_sq * 0.5) >> 32);
+    {
+        const uint32_t h = (uint32_t)(double_bits(std::sqrt(p.limit_sq * 0.5)) >> 32);
+        p.filter_abs_hi = h ? h - 1u : 0u;
+    }
     p.chunk = kDefaultChunk;
     p.chunks_per_row = cfg.width ? (cfg.width + p.chunk - 1) / p.chunk : 0;
     const uint64_t npix = (uint64_t)p.rows * cfg.width;
@@ -367,7 +371,10 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     plan->npix = npix;
     plan->out_bytes = (size_t)npix * format;
     uint32_t v = tl_variant;
-    if (v == FRB_KERNEL_AUTO) v = sparse_is_safe(cfg) ? FRB_KERNEL_STREAM6 : (form6_is_exact(cfg) ? FRB_KERNEL_DENSE6 : FRB_KERNEL_STREAM7);
+    // A forced variant is a request: outside its proven domain it is downgraded to the next kernel that is exact
+    // (STREAM6 -> DENSE6 -> STREAM7); FrbStats.kernel_variant reports what actually ran.
+    if (v == FRB_KERNEL_AUTO || v == FRB_KERNEL_STREAM6) v = sparse_is_safe(cfg) ? FRB_KERNEL_STREAM6 : FRB_KERNEL_DENSE6;
+    if (v == FRB_KERNEL_DENSE6 && !form6_is_exact(cfg)) v = FRB_KERNEL_STREAM7;
     plan->variant = v;
 
     if (int rc = ensure(c.tab, c.tab_cap, (size_t)cfg.width + cfg.height + 2)) return rc;
@@ -437,6 +444,11 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
         frb::frb_shade_kernel<<<grid, frb::kShadeThreads, 0, st>>>(p);
         slot.launches++;
         slot.shaded = true;
+    }
+    else if (plan.npix > 0) {
+        const uint32_t grid = (uint32_t)std::min<uint64_t>((plan.npix + 255) / 256, (uint64_t)c.sm_count * 16);
+        frb::frb_sum_iterations_kernel<<<grid, 256, 0, st>>>(p);
+        slot.launches++;
     }
     CU(cudaEventRecord(slot.ev_shade, st));
     if (plan.npix > 0) CU(cudaMemcpyAsync(slot.host, c.stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, st));

@@ -51,7 +51,7 @@ struct RenderParams {
     uint32_t primary;      // stored fields r | g<<8 | b<<16
     uint32_t secondary;
     uint32_t format;       // 3 = RGB24, 4 = RGBA32
-    uint32_t pad0;
+    uint32_t filter_abs_hi; // high word of sqrt(S/2), minus 1: max(|re|,|im|) >= this is necessary for re^2+im^2 > S/2
     // buffers
     double *tab_re;              // [width]   re0(x)
     double *tab_im;              // [height]  im0(y), indexed by IMAGE row
@@ -214,7 +214,6 @@ frb_iterate_stream_kernel(const __grid_constant__ RenderParams p)
     uint32_t next_chunk = 0;
     if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
 
-    unsigned long long useful = 0;  // loop-body executions of finished pixels (per lane)
     uint32_t trips = 0;             // lock-step blocks issued by this warp
 
     for (;;) {
@@ -303,19 +302,13 @@ frb_iterate_stream_kernel(const __grid_constant__ RenderParams p)
                 // recursive() returns (next, i) on escape, (previous, iterations) otherwise: (o.x, o.y) is that position
                 p.iters[pix] = count;
                 p.zfinal[pix] = make_double2(o.x, o.y);
-                useful += (count < iterations) ? (unsigned long long)count + 1ull : (unsigned long long)iterations;
                 active = false;
             }
         }
     }
 
-    // statistics: one atomic per warp
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) useful += __shfl_xor_sync(FULL, useful, s);
-    if (lane == 0) {
-        atomicAdd(p.stats + 0, useful);
-        atomicAdd(p.stats + 1, (unsigned long long)trips * (unsigned long long)(32 * kUnroll));
-    }
+    // statistics: one atomic per warp (the useful-iteration total is summed by the shade / sum kernel)
+    if (lane == 0) atomicAdd(p.stats + 1, (unsigned long long)trips * (unsigned long long)(32 * kUnroll));
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -327,16 +320,22 @@ frb_iterate_stream_kernel(const __grid_constant__ RenderParams p)
 // of kSparseU iterations; each step's position is left in its own registers (hx[k], hy[k]: no moves, the unrolled
 // block simply rotates registers) and ONE filter per block tests the last step's squares.
 //
-// Why one test per block suffices (host-checked precondition, frb_api.cu: sparse_is_safe): with R = limit >= 4
-// and |c| <= R^2 - 3R for every pixel, once |z_k|^2 > S = R^2 every later step has |z_m| >= |z_{m-1}|^2 - |c| >= 2R,
-// i.e. max(re^2, im^2) >= 2S, growing doubly exponentially to +inf and then NaN (inf - inf) — all of which pass
-// the unsigned high-word filter.  So "filter fails at the end of the block" proves no step of the block escaped.
-// When it fires, the exact reference test (re^2 + im^2 > S, same products, same sum) is replayed on the recorded
-// positions to find the first escaping step; the reference's count and final position come out bit-identical.
+// Why one test per block suffices (host-checked precondition, frb_api.cu: sparse_is_safe): with R = limit >= 8
+// and |c| <= R^2/2 - 3R for every pixel, a step with max(re^2, im^2) >= S/2 (S = R^2) is followed by
+// |z_{m}| >= |z_{m-1}|^2 - |c| >= 3R, i.e. by escaped steps only, growing doubly exponentially to +inf and then NaN
+// (inf - inf) — all of which pass the unsigned high-word filter.  So "filter fails at the end of the block"
+// proves no step of the block escaped, and "first step that passes the necessary condition" is monotone in k.
+// When the block-end filter fires, that first step is found by an integer binary search over the recorded
+// positions and the exact reference test (re^2 + im^2 > S, same products, same sum) is evaluated on it (and on the
+// next step if it was a near miss); the reference's count and final position come out bit-identical.
 // A lane whose block-end filter fired without any step escaping (S/2 <= max < S) just carries on.
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kSparseU = 8;
 constexpr uint32_t kIdleLeft = 0x80000000u;  // "iterations left" of a lane without a pixel (zero orbit, never attends)
+
+__device__ __forceinline__ uint32_t abs_hi(double v) { return (uint32_t)__double2hiint(v) & 0x7fffffffu; }
+
+__device__ __forceinline__ double sel_d(bool c, double a, double b) { return c ? a : b; }
 
 template <int FORM>
 __global__ void __launch_bounds__(kIterateThreads, 3)
@@ -344,22 +343,21 @@ frb_iterate_sparse_kernel(const __grid_constant__ RenderParams p)
 {
     constexpr unsigned FULL = 0xffffffffu;
     constexpr uint32_t U = (uint32_t)kSparseU;
+    static_assert(kSparseU == 8, "the resolve tree below is written for blocks of 8");
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
 
     const double S = p.limit_sq;
     const uint32_t filter_hi = p.filter_hi;
     const uint32_t iterations = p.iterations;
-    const bool julia = (p.algo == kAlgoJulia);
 
     Orbit o = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     double hx[kSparseU], hy[kSparseU];
-#pragma unroll
-    for (int k = 0; k < kSparseU; ++k) hx[k] = hy[k] = 0.0;
-    uint32_t left = kIdleLeft;  // iterations still to run for the lane's pixel
+    // A lane without a pixel runs the zero orbit (never fires the filter).  left = U makes every lane ask for
+    // service after the first (dummy) block, which is how the first pixels are handed out.
+    uint32_t left = U;
     uint32_t pix = 0;
     bool active = false;
-    bool cand = false;          // the last block's end-of-block filter fired for this lane
 
     uint32_t cur_x = 0, cur_end = 0, cur_rowpix = 0;
     double cur_im = 0.0;
@@ -367,123 +365,127 @@ frb_iterate_sparse_kernel(const __grid_constant__ RenderParams p)
     uint32_t next_chunk = 0;
     if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
 
-    unsigned long long useful = 0;
-    unsigned long long trips = 0;       // lock-step blocks issued by this warp (every lane counts the same)
+    unsigned long long lane_slots = 0;  // iterations issued per lane slot (same for every lane of the warp)
     uint32_t left_mark = left;
 
     for (;;) {
-        // ------------------------------ service (cold) ------------------------------
-        trips += (unsigned long long)((left_mark - left) / U);
-        for (;;) {
-            bool done = false;
-            uint32_t count = iterations;
-            if (active) {
-                if (cand) {
-                    // replay the reference's test on the recorded steps of the last block
-                    const uint32_t i0 = iterations - (left + U);  // index of the block's first iteration
-                    bool found = false;
+        // ------------------------------ hot ------------------------------
+        // Per block: kSparseU x 6 FP64 instructions, then IADD, VIMNMX, 2 x ISETP, VOTE, BRA.
 #pragma unroll
-                    for (int k = 0; k < kSparseU; ++k) {
-                        if (!found) {
-                            const double xa = __dmul_rn(hx[k], hx[k]);
-                            const double yb = __dmul_rn(hy[k], hy[k]);
-                            const uint32_t m = max((uint32_t)__double2hiint(xa), (uint32_t)__double2hiint(yb));
-                            if (m >= filter_hi && __dadd_rn(xa, yb) > S) {
-                                found = true;
-                                count = i0 + (uint32_t)k;
-                                o.x = hx[k];
-                                o.y = hy[k];
-                            }
-                        }
-                    }
-                    done = found;
-                }
-                if (!done && left < U) {
-                    // fewer than U iterations left: finish with the per-iteration test
-                    done = true;
-                    const uint32_t i0 = iterations - left;
-                    for (uint32_t k = 0; k < left; ++k) {
-                        stream_core<FORM>(o);
-                        if (stream_filter(o, filter_hi) && stream_escaped(o, S)) {
-                            count = i0 + k;
-                            break;
-                        }
-                    }
-                }
-                if (done) {
-                    p.iters[pix] = count;
-                    p.zfinal[pix] = make_double2(o.x, o.y);
-                    useful += (count < iterations) ? (unsigned long long)count + 1ull : (unsigned long long)iterations;
-                    active = false;
+        for (int k = 0; k < kSparseU; ++k) {
+            stream_core<FORM>(o);
+            hx[k] = o.x;
+            hy[k] = o.y;
+        }
+        left -= U;
+        const bool cand = stream_filter(o, filter_hi);
+        if (!__any_sync(FULL, cand || (left < U))) continue;
+
+        // ------------------------------ service (cold) ------------------------------
+        lane_slots += (unsigned long long)(left_mark - left);
+        bool done = false;
+        uint32_t count = iterations;
+        if (cand) {
+            // First step k of the block whose position passes the necessary condition max(|re|,|im|) >= sqrt(S/2)
+            // (monotone in k under sparse_is_safe: a passing step is followed by escaped steps only).
+            // Binary search with the positions selected along the way; no FP64 until the single exact test.
+            const uint32_t t2 = p.filter_abs_hi;
+            const bool b2 = max(abs_hi(hx[3]), abs_hi(hy[3])) < t2;       // first pass is in 4..7
+            const double x0 = sel_d(b2, hx[4], hx[0]), x1 = sel_d(b2, hx[5], hx[1]), x2 = sel_d(b2, hx[6], hx[2]), x3 = sel_d(b2, hx[7], hx[3]);
+            const double y0 = sel_d(b2, hy[4], hy[0]), y1 = sel_d(b2, hy[5], hy[1]), y2 = sel_d(b2, hy[6], hy[2]), y3 = sel_d(b2, hy[7], hy[3]);
+            const bool b1 = max(abs_hi(x1), abs_hi(y1)) < t2;             // ... in the upper pair of that half
+            const double u0 = sel_d(b1, x2, x0), u1 = sel_d(b1, x3, x1);
+            const double v0 = sel_d(b1, y2, y0), v1 = sel_d(b1, y3, y1);
+            const bool b0 = max(abs_hi(u0), abs_hi(v0)) < t2;
+            double zx = sel_d(b0, u1, u0), zy = sel_d(b0, v1, v0);
+            uint32_t k = (b2 ? 4u : 0u) + (b1 ? 2u : 0u) + (b0 ? 1u : 0u);
+            // the reference's test on that step: same products, same sum, same compare
+            bool esc = __dadd_rn(__dmul_rn(zx, zx), __dmul_rn(zy, zy)) > S;
+            if (!esc && k < U - 1) {
+                // the passing step had S/2 <= max < S without escaping: the next one is the first that can have
+                ++k;
+                zx = hx[1]; zy = hy[1];
+                if (k == 2) { zx = hx[2]; zy = hy[2]; }
+                if (k == 3) { zx = hx[3]; zy = hy[3]; }
+                if (k == 4) { zx = hx[4]; zy = hy[4]; }
+                if (k == 5) { zx = hx[5]; zy = hy[5]; }
+                if (k == 6) { zx = hx[6]; zy = hy[6]; }
+                if (k == 7) { zx = hx[7]; zy = hy[7]; }
+                esc = __dadd_rn(__dmul_rn(zx, zx), __dmul_rn(zy, zy)) > S;
+            }
+            if (esc) {
+                done = true;
+                count = iterations - (left + U) + k;  // block's first iteration index + k
+                o.x = zx;
+                o.y = zy;
+            }
+        }
+        if (!done && active && left < U) {
+            // fewer than U iterations left: finish with the per-iteration test
+            done = true;
+            const uint32_t i0 = iterations - left;
+            for (uint32_t k = 0; k < left; ++k) {
+                stream_core<FORM>(o);
+                if (stream_filter(o, filter_hi) && stream_escaped(o, S)) {
+                    count = i0 + k;
+                    break;
                 }
             }
-            cand = false;
+        }
+        if (done) {
+            // recursive() returns (next, i) on escape, (previous, iterations) otherwise
+            p.iters[pix] = count;
+            p.zfinal[pix] = make_double2(o.x, o.y);
+            active = false;
+        }
+        unsigned need = __ballot_sync(FULL, !active);
+        while (need != 0u && !drained) {
+            if (cur_x == cur_end) {
+                const uint32_t c = __shfl_sync(FULL, next_chunk, 0);
+                if (c >= p.total_chunks) {
+                    drained = true;
+                    break;
+                }
+                if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
+                const uint32_t lr = c / p.chunks_per_row;
+                const uint32_t seg = c - lr * p.chunks_per_row;
+                cur_x = seg * p.chunk;
+                cur_end = min(cur_x + p.chunk, p.width);
+                cur_rowpix = lr * p.width;
+                cur_im = __ldg(p.tab_im + local_row_to_y(p, lr));
+            }
+            const uint32_t avail = cur_end - cur_x;
+            const uint32_t rank = __popc(need & lt_mask);
+            if (!active && rank < avail) {
+                const uint32_t px = cur_x + rank;
+                const double re0 = __ldg(p.tab_re + px);
+                // get_recursive_pixel (calc/src/lib.rs:208-210): Mandelbrot c = start, Julia c = julia_set
+                const bool julia = (p.algo == kAlgoJulia);
+                o.x = re0;
+                o.y = cur_im;
+                o.cr = julia ? p.julia_re : re0;
+                o.ci = julia ? p.julia_im : cur_im;
+                o.a = __dmul_rn(re0, re0);
+                o.b = __dmul_rn(cur_im, cur_im);
+                left = iterations;
+                pix = cur_rowpix + px;
+                active = true;
+            }
+            cur_x += min((uint32_t)__popc(need), avail);
+            need = __ballot_sync(FULL, !active);
+        }
+        if (need != 0u) {
+            // queue drained: lanes without a pixel park on the zero orbit; the warp leaves when all are parked
+            if (need == FULL) break;
             if (!active) {
-                // park: zero orbit never fires the filter; kIdleLeft never runs out
                 o.x = o.y = o.a = o.b = o.cr = o.ci = 0.0;
                 left = kIdleLeft;
             }
-            unsigned need = __ballot_sync(FULL, !active);
-            while (!drained && need != 0u) {
-                if (cur_x == cur_end) {
-                    const uint32_t c = __shfl_sync(FULL, next_chunk, 0);
-                    if (c >= p.total_chunks) {
-                        drained = true;
-                        break;
-                    }
-                    if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
-                    const uint32_t lr = c / p.chunks_per_row;
-                    const uint32_t seg = c - lr * p.chunks_per_row;
-                    cur_x = seg * p.chunk;
-                    cur_end = min(cur_x + p.chunk, p.width);
-                    cur_rowpix = lr * p.width;
-                    cur_im = __ldg(p.tab_im + local_row_to_y(p, lr));
-                }
-                const uint32_t avail = cur_end - cur_x;
-                const uint32_t rank = __popc(need & lt_mask);
-                if (!active && rank < avail) {
-                    const uint32_t px = cur_x + rank;
-                    const double re0 = __ldg(p.tab_re + px);
-                    o.x = re0;
-                    o.y = cur_im;
-                    o.cr = julia ? p.julia_re : re0;
-                    o.ci = julia ? p.julia_im : cur_im;
-                    o.a = __dmul_rn(re0, re0);
-                    o.b = __dmul_rn(cur_im, cur_im);
-                    left = iterations;
-                    pix = cur_rowpix + px;
-                    active = true;
-                }
-                cur_x += min((uint32_t)__popc(need), avail);
-                need = __ballot_sync(FULL, !active);
-            }
-            if (need == FULL) goto finished;                       // drained, nothing in flight
-            if (!__any_sync(FULL, active && left < U)) break;      // everyone can run a full block
         }
         left_mark = left;
+    }
 
-        // ------------------------------ hot ------------------------------
-        // Per block: kSparseU x 6 FP64 instructions, then IADD, VIMNMX, 2 x ISETP, VOTE, BRA.
-        bool attn;
-        do {
-#pragma unroll
-            for (int k = 0; k < kSparseU; ++k) {
-                stream_core<FORM>(o);
-                hx[k] = o.x;
-                hy[k] = o.y;
-            }
-            left -= U;
-            cand = stream_filter(o, filter_hi);
-            attn = cand || (left < U);
-        } while (!__any_sync(FULL, attn));
-    }
-finished:
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) useful += __shfl_xor_sync(FULL, useful, s);
-    if (lane == 0) {
-        atomicAdd(p.stats + 0, useful);
-        atomicAdd(p.stats + 1, trips * (unsigned long long)(32 * kSparseU));
-    }
+    if (lane == 0) atomicAdd(p.stats + 1, lane_slots * 32ull);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -498,7 +500,6 @@ frb_iterate_simple_kernel(const __grid_constant__ RenderParams p)
     const uint32_t x = blockIdx.y * blockDim.x + threadIdx.x;
     const uint32_t lr = blockIdx.x;
     const bool valid = (x < p.width) && (lr < p.rows);
-    unsigned long long useful = 0;
     if (valid) {
         const double re0 = p.tab_re[x];
         const double im0 = p.tab_im[local_row_to_y(p, lr)];
@@ -515,11 +516,7 @@ frb_iterate_simple_kernel(const __grid_constant__ RenderParams p)
         const uint32_t pix = lr * p.width + x;
         p.iters[pix] = count;
         p.zfinal[pix] = make_double2(o.x, o.y);
-        useful = (count < p.iterations) ? (unsigned long long)count + 1ull : (unsigned long long)p.iterations;
     }
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) useful += __shfl_xor_sync(0xffffffffu, useful, s);
-    if ((threadIdx.x & 31u) == 0 && useful != 0ull) atomicAdd(p.stats + 0, useful);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -571,6 +568,7 @@ frb_shade_kernel(const __grid_constant__ RenderParams p)
     const uint64_t npix = (uint64_t)p.rows * p.width;
     const uint64_t cta_px = (uint64_t)kShadeThreads * kShadePxPerThread;
     const uint64_t nblocks = (npix + cta_px - 1) / cta_px;
+    unsigned long long useful = 0;  // loop-body executions of calc::recursive: i+1 for an escape at index i, else iterations
     for (uint64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const uint64_t base = blk * cta_px + (uint64_t)threadIdx.x * kShadePxPerThread;
         uint32_t c[4] = {0u, 0u, 0u, 0u};
@@ -578,11 +576,18 @@ frb_shade_kernel(const __grid_constant__ RenderParams p)
             const uint4 n4 = *reinterpret_cast<const uint4 *>(p.iters + base);
             const uint32_t n[4] = {n4.x, n4.y, n4.z, n4.w};
 #pragma unroll
-            for (int k = 0; k < 4; ++k) c[k] = shade_pixel(p, n[k], p.zfinal[base + k]);
+            for (int k = 0; k < 4; ++k) {
+                c[k] = shade_pixel(p, n[k], p.zfinal[base + k]);
+                useful += min(n[k], p.iterations - 1u) + 1u;
+            }
         } else {
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-                if (base + k < npix) c[k] = shade_pixel(p, p.iters[base + k], p.zfinal[base + k]);
+                if (base + k < npix) {
+                    const uint32_t n = p.iters[base + k];
+                    c[k] = shade_pixel(p, n, p.zfinal[base + k]);
+                    useful += min(n, p.iterations - 1u) + 1u;
+                }
         }
         const bool full_cta = (blk + 1) * cta_px <= npix;
         if (p.format == 4u) {
@@ -615,6 +620,24 @@ frb_shade_kernel(const __grid_constant__ RenderParams p)
             }
         }
     }
+    if (p.iterations == 0u || p.algo == kAlgoFern) useful = 0;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) useful += __shfl_xor_sync(0xffffffffu, useful, s);
+    if ((threadIdx.x & 31u) == 0 && useful != 0ull) atomicAdd(p.stats + 0, useful);
+}
+
+// Sum of loop-body executions when no image is shaded (frb_render_counts).
+__global__ void __launch_bounds__(256)
+frb_sum_iterations_kernel(const __grid_constant__ RenderParams p)
+{
+    const uint64_t npix = (uint64_t)p.rows * p.width;
+    unsigned long long useful = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (uint64_t)gridDim.x * blockDim.x)
+        useful += min(p.iters[i], p.iterations - 1u) + 1u;
+    if (p.iterations == 0u || p.algo == kAlgoFern) useful = 0;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) useful += __shfl_xor_sync(0xffffffffu, useful, s);
+    if ((threadIdx.x & 31u) == 0 && useful != 0ull) atomicAdd(p.stats + 0, useful);
 }
 
 }  // namespace frb

@@ -125,7 +125,7 @@ typedef struct FrbStats {
 enum {
     FRB_KERNEL_AUTO = 0,      /* STREAM6 when its preconditions hold (every sane input), else DENSE6, else STREAM7 */
     FRB_KERNEL_STREAM6 = 1,   /* persistent lane-refill kernel, 6 FP64 instructions / iteration, one escape filter per
-                                 block of 8 iterations (needs limit >= 4 and |c| <= limit^2 - 3 limit: an escaped orbit
+                                 block of 8 iterations (needs limit >= 8 and |c| <= limit^2/2 - 3 limit: an escaped orbit
                                  then provably keeps growing) */
     FRB_KERNEL_STREAM7 = 2,   /* persistent lane-refill kernel, 7 FP64 instructions / iteration, filter every
                                  iteration: exact for ANY input */
