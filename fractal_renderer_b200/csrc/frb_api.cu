@@ -134,7 +134,7 @@ int ctx_init(DeviceCtx *c, int dev)
                                                      frb::kIterateThreads, 0));
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->iter_blocks_per_sm[1], frb::frb_iterate_stream_kernel<7>,
                                                      frb::kIterateThreads, 0));
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->iter_blocks_per_sm[2], frb::frb_iterate_sparse_kernel<6>,
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->iter_blocks_per_sm[2], frb::frb_iterate_sparse_kernel<6, false>,
                                                      frb::kIterateThreads, 0));
     if (c->iter_blocks_per_sm[0] < 1 || c->iter_blocks_per_sm[1] < 1 || c->iter_blocks_per_sm[2] < 1)
         return fail(FRB_ERR_CUDA, "iterate kernel does not fit on device %d", dev);
@@ -299,6 +299,7 @@ bool sparse_is_safe(const FrbConfig &cfg)
 {
     if (!form6_is_exact(cfg)) return false;
     if (cfg.iterations < 4u * (uint32_t)frb::kSparseU) return false;  // too short to amortise a block
+    if (cfg.iterations >= frb::kIdleBit) return false;                // the kernel encodes "idle lane" in the counter's top bits
     const double R = std::fabs(cfg.limit);
     if (!(R >= 8.0) || !(R <= 1e150)) return false;
     double cmax;
@@ -426,8 +427,10 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
                     frb::frb_iterate_stream_kernel<6><<<blocks, frb::kIterateThreads, 0, st>>>(p);
                 else if (kidx == 1)
                     frb::frb_iterate_stream_kernel<7><<<blocks, frb::kIterateThreads, 0, st>>>(p);
+                else if (p.algo == FRB_ALGO_JULIA)
+                    frb::frb_iterate_sparse_kernel<6, true><<<blocks, frb::kIterateThreads, 0, st>>>(p);
                 else
-                    frb::frb_iterate_sparse_kernel<6><<<blocks, frb::kIterateThreads, 0, st>>>(p);
+                    frb::frb_iterate_sparse_kernel<6, false><<<blocks, frb::kIterateThreads, 0, st>>>(p);
             }
             slot.launches++;
         } else {

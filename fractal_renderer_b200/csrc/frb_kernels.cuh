@@ -331,14 +331,16 @@ frb_iterate_stream_kernel(const __grid_constant__ RenderParams p)
 // A lane whose block-end filter fired without any step escaping (S/2 <= max < S) just carries on.
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kSparseU = 8;
-constexpr uint32_t kIdleLeft = 0x80000000u;  // "iterations left" of a lane without a pixel (zero orbit, never attends)
 
 __device__ __forceinline__ uint32_t abs_hi(double v) { return (uint32_t)__double2hiint(v) & 0x7fffffffu; }
 
 __device__ __forceinline__ double sel_d(bool c, double a, double b) { return c ? a : b; }
 
-template <int FORM>
-__global__ void __launch_bounds__(kIterateThreads, 3)
+// A lane is idle (holds no pixel) iff left >= kIdleBit; the host only selects this kernel for iterations < 2^30.
+constexpr uint32_t kIdleBit = 0x40000000u;
+
+template <int FORM, bool JULIA>
+__global__ void __launch_bounds__(kIterateThreads, 4)
 frb_iterate_sparse_kernel(const __grid_constant__ RenderParams p)
 {
     constexpr unsigned FULL = 0xffffffffu;
@@ -349,15 +351,13 @@ frb_iterate_sparse_kernel(const __grid_constant__ RenderParams p)
 
     const double S = p.limit_sq;
     const uint32_t filter_hi = p.filter_hi;
-    const uint32_t iterations = p.iterations;
 
     Orbit o = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     double hx[kSparseU], hy[kSparseU];
-    // A lane without a pixel runs the zero orbit (never fires the filter).  left = U makes every lane ask for
-    // service after the first (dummy) block, which is how the first pixels are handed out.
-    uint32_t left = U;
+    // A lane without a pixel runs the zero orbit (never fires the filter) with left >= kIdleBit.  Every lane starts
+    // idle, so the first pass through the service code below is a pure refill.
+    uint32_t left = kIdleBit * 2u;
     uint32_t pix = 0;
-    bool active = false;
 
     uint32_t cur_x = 0, cur_end = 0, cur_rowpix = 0;
     double cur_im = 0.0;
@@ -367,22 +367,14 @@ frb_iterate_sparse_kernel(const __grid_constant__ RenderParams p)
 
     unsigned long long lane_slots = 0;  // iterations issued per lane slot (same for every lane of the warp)
     uint32_t left_mark = left;
+    bool cand = false;
+#pragma unroll
+    for (int k = 0; k < kSparseU; ++k) hx[k] = hy[k] = 0.0;
 
     for (;;) {
-        // ------------------------------ hot ------------------------------
-        // Per block: kSparseU x 6 FP64 instructions, then IADD, VIMNMX, 2 x ISETP, VOTE, BRA.
-#pragma unroll
-        for (int k = 0; k < kSparseU; ++k) {
-            stream_core<FORM>(o);
-            hx[k] = o.x;
-            hy[k] = o.y;
-        }
-        left -= U;
-        const bool cand = stream_filter(o, filter_hi);
-        if (!__any_sync(FULL, cand || (left < U))) continue;
-
         // ------------------------------ service (cold) ------------------------------
         lane_slots += (unsigned long long)(left_mark - left);
+        const uint32_t iterations = p.iterations;
         bool done = false;
         uint32_t count = iterations;
         if (cand) {
@@ -420,8 +412,8 @@ frb_iterate_sparse_kernel(const __grid_constant__ RenderParams p)
                 o.y = zy;
             }
         }
-        if (!done && active && left < U) {
-            // fewer than U iterations left: finish with the per-iteration test
+        if (!done && left < U) {
+            // fewer than U iterations left (idle lanes have left >= kIdleBit): finish with the per-iteration test
             done = true;
             const uint32_t i0 = iterations - left;
             for (uint32_t k = 0; k < left; ++k) {
@@ -436,53 +428,88 @@ frb_iterate_sparse_kernel(const __grid_constant__ RenderParams p)
             // recursive() returns (next, i) on escape, (previous, iterations) otherwise
             p.iters[pix] = count;
             p.zfinal[pix] = make_double2(o.x, o.y);
-            active = false;
+            left = kIdleBit * 2u;
         }
-        unsigned need = __ballot_sync(FULL, !active);
-        while (need != 0u && !drained) {
-            if (cur_x == cur_end) {
-                const uint32_t c = __shfl_sync(FULL, next_chunk, 0);
-                if (c >= p.total_chunks) {
-                    drained = true;
-                    break;
-                }
-                if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
-                const uint32_t lr = c / p.chunks_per_row;
-                const uint32_t seg = c - lr * p.chunks_per_row;
-                cur_x = seg * p.chunk;
-                cur_end = min(cur_x + p.chunk, p.width);
-                cur_rowpix = lr * p.width;
-                cur_im = __ldg(p.tab_im + local_row_to_y(p, lr));
-            }
-            const uint32_t avail = cur_end - cur_x;
-            const uint32_t rank = __popc(need & lt_mask);
-            if (!active && rank < avail) {
-                const uint32_t px = cur_x + rank;
-                const double re0 = __ldg(p.tab_re + px);
-                // get_recursive_pixel (calc/src/lib.rs:208-210): Mandelbrot c = start, Julia c = julia_set
-                const bool julia = (p.algo == kAlgoJulia);
-                o.x = re0;
-                o.y = cur_im;
-                o.cr = julia ? p.julia_re : re0;
-                o.ci = julia ? p.julia_im : cur_im;
-                o.a = __dmul_rn(re0, re0);
-                o.b = __dmul_rn(cur_im, cur_im);
-                left = iterations;
-                pix = cur_rowpix + px;
-                active = true;
-            }
-            cur_x += min((uint32_t)__popc(need), avail);
-            need = __ballot_sync(FULL, !active);
-        }
+        unsigned need = __ballot_sync(FULL, left >= kIdleBit);
         if (need != 0u) {
-            // queue drained: lanes without a pixel park on the zero orbit; the warp leaves when all are parked
-            if (need == FULL) break;
-            if (!active) {
-                o.x = o.y = o.a = o.b = o.cr = o.ci = 0.0;
-                left = kIdleLeft;
+            if (!drained) {
+                const uint32_t n = (uint32_t)__popc(need);
+                if (cur_end - cur_x >= n) {
+                    // fast path: the warp's current row segment covers every free lane
+                    if (left >= kIdleBit) {
+                        const uint32_t px = cur_x + (uint32_t)__popc(need & lt_mask);
+                        const double re0 = __ldg(p.tab_re + px);
+                        // get_recursive_pixel (calc/src/lib.rs:208-210): Mandelbrot c = start, Julia c = julia_set
+                        o.x = re0;
+                        o.y = cur_im;
+                        o.cr = JULIA ? p.julia_re : re0;
+                        o.ci = JULIA ? p.julia_im : cur_im;
+                        o.a = __dmul_rn(re0, re0);
+                        o.b = __dmul_rn(cur_im, cur_im);
+                        left = iterations;
+                        pix = cur_rowpix + px;
+                    }
+                    cur_x += n;
+                    need = 0u;
+                } else {
+                    // generic path: spans a segment boundary and/or fetches the next chunk from the queue
+                    while (need != 0u) {
+                        if (cur_x == cur_end) {
+                            const uint32_t c = __shfl_sync(FULL, next_chunk, 0);
+                            if (c >= p.total_chunks) {
+                                drained = true;
+                                break;
+                            }
+                            if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
+                            const uint32_t lr = c / p.chunks_per_row;
+                            const uint32_t seg = c - lr * p.chunks_per_row;
+                            cur_x = seg * p.chunk;
+                            cur_end = min(cur_x + p.chunk, p.width);
+                            cur_rowpix = lr * p.width;
+                            cur_im = __ldg(p.tab_im + local_row_to_y(p, lr));
+                        }
+                        const uint32_t avail = cur_end - cur_x;
+                        const uint32_t rank = __popc(need & lt_mask);
+                        if (left >= kIdleBit && rank < avail) {
+                            const uint32_t px = cur_x + rank;
+                            const double re0 = __ldg(p.tab_re + px);
+                            o.x = re0;
+                            o.y = cur_im;
+                            o.cr = JULIA ? p.julia_re : re0;
+                            o.ci = JULIA ? p.julia_im : cur_im;
+                            o.a = __dmul_rn(re0, re0);
+                            o.b = __dmul_rn(cur_im, cur_im);
+                            left = iterations;
+                            pix = cur_rowpix + px;
+                        }
+                        cur_x += min((uint32_t)__popc(need), avail);
+                        need = __ballot_sync(FULL, left >= kIdleBit);
+                    }
+                }
+            }
+            if (need != 0u) {
+                // queue drained: lanes without a pixel park on the zero orbit; the warp leaves when all are parked
+                if (need == FULL) break;
+                if (left >= kIdleBit) {
+                    o.x = o.y = o.a = o.b = o.cr = o.ci = 0.0;
+                    left = kIdleBit * 2u;
+                }
             }
         }
         left_mark = left;
+
+        // ------------------------------ hot ------------------------------
+        // Per block: kSparseU x 6 FP64 instructions, then IADD, VIMNMX, 2 x ISETP, VOTE, BRA.
+        do {
+#pragma unroll
+            for (int k = 0; k < kSparseU; ++k) {
+                stream_core<FORM>(o);
+                hx[k] = o.x;
+                hy[k] = o.y;
+            }
+            left -= U;
+            cand = stream_filter(o, filter_hi);
+        } while (!__any_sync(FULL, cand || (left < U)));
     }
 
     if (lane == 0) atomicAdd(p.stats + 1, lane_slots * 32ull);
