@@ -120,10 +120,20 @@ def cpu_sample_rows(height: int, stride: int):
     return np.arange(stride // 2, height, stride, dtype=np.uint32)
 
 
+def host_threads() -> int:
+    """All host cores this process may use — NOT omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def time_cpu(cfg, stride: int, threads: int = 0):
     """Oracle (OpenMP rows, like rayon) on a row-strided sample of the frame.  Returns (G iter/s, seconds, iterations)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_binding as ob
+
+    threads = threads or host_threads()
 
     rows = cpu_sample_rows(cfg.height, stride)
     t = time.perf_counter()
@@ -136,7 +146,7 @@ def cpu_baseline(cfg) -> dict:
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_binding as ob
 
-    cores = ob.max_threads()
+    cores = host_threads()
     stride = 16
     g, dt, iters, nrows = time_cpu(cfg, stride)
     # grow the sample until it is ~10 s of CPU work (bounded: never more than the whole frame)
@@ -157,7 +167,7 @@ def run_reference(args, cfg, total_iterations):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_binding as ob
 
-    cores = ob.max_threads()
+    cores = host_threads()
     # size the per-step sample to ~1-2 s so that K+W steps finish within a few minutes on any core count
     stride = 16
     g, dt, iters, nrows = time_cpu(cfg, stride)
@@ -330,10 +340,18 @@ def main():
     form = {frb.KERNEL_STREAM6: 6, frb.KERNEL_DENSE6: 6, frb.KERNEL_STREAM7: 7}.get(kernel_variant, 11)
     kname = {frb.KERNEL_STREAM6: "frb_iterate_sparse_kernel<6>", frb.KERNEL_DENSE6: "frb_iterate_stream_kernel<6>",
              frb.KERNEL_STREAM7: "frb_iterate_stream_kernel<7>"}.get(kernel_variant, "frb_iterate_simple_kernel")
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json"))).get(args.workload)
+        if tj and tj["kernel"] == kname and world == 1:
+            traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+    except (OSError, ValueError, KeyError):
+        pass
     roofline = {
         "bound": "fp64",
         "achieved": round(achieved_tflops, 3), "peak": round(peak_tflops, 3), "unit": "TFLOP/s",
-        "frac": round(achieved_tflops / peak_tflops, 4), "traffic": None,
+        "frac": round(achieved_tflops / peak_tflops, 4), "traffic": traffic,
+        "traffic_note": "DRAM bytes read+written by this kernel per launch from one ncu --set full capture (profiles/r1_traffic.json); algorithmic = 20 B/px raw result written, 0 read",
         "kernel": kname,
         "kernel_ms": round(it_ms, 4), "shade_kernel_ms": round(statistics.mean(shade_ms), 4),
         "kernel_share_of_step": round(it_ms * args.steps / dev_ms, 4) if world == 1 else None,
@@ -342,7 +360,7 @@ def main():
         "fp64_instr_per_iter": form,
         "pipe_frac": round(per_launch_iters * form / (it_ms * 1e-3) / peak["dfma_per_s"], 4),
         "lane_utilisation": round(my_iters / lane_iters, 4) if lane_iters else None,
-        "peak_detail": {k: (round(v / 1e12, 3) if k.endswith("_per_s") else v) for k, v in peak.items()},
+        "peak_detail": {k: round(v / 1e12, 3) for k, v in peak.items() if k.endswith("_per_s")},
         "note": "bound is the FP64 pipe (scalar recurrence, 3 B written per ~1400 iterations): HBM and tensor rooflines do not apply; "
                 "achieved counts the reference's 10 flop/iteration, the kernel issues fp64_instr_per_iter FP64 instructions per iteration "
                 "(pipe_frac = FP64 instructions issued for useful iterations / measured DFMA instruction peak)",
