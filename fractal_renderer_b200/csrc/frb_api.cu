@@ -11,6 +11,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -134,7 +135,7 @@ int ctx_init(DeviceCtx *c, int dev)
                                                      frb::kIterateThreads, 0));
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->iter_blocks_per_sm[1], frb::frb_iterate_stream_kernel<7>,
                                                      frb::kIterateThreads, 0));
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->iter_blocks_per_sm[2], frb::frb_iterate_sparse_kernel<6, false>,
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->iter_blocks_per_sm[2], frb::frb_iterate_sparse_kernel<false, 8>,
                                                      frb::kIterateThreads, 0));
     if (c->iter_blocks_per_sm[0] < 1 || c->iter_blocks_per_sm[1] < 1 || c->iter_blocks_per_sm[2] < 1)
         return fail(FRB_ERR_CUDA, "iterate kernel does not fit on device %d", dev);
@@ -349,7 +350,10 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
         const uint32_t h = (uint32_t)(double_bits(std::sqrt(p.limit_sq * 0.5)) >> 32);
         p.filter_abs_hi = h ? h - 1u : 0u;
     }
-    p.chunk = kDefaultChunk;
+    // 32-pixel segments balance the end of a long-iteration frame better (C2: 5.00 vs 5.09 ms); short-iteration frames
+    // (C1, C3) prefer fewer queue transactions (measured, profiles/r1_tuning_sweeps.txt)
+    p.chunk = cfg.iterations >= 2048u ? 32u : kDefaultChunk;
+    if (const char *e = getenv("FRB_TUNE_CHUNK")) p.chunk = std::max(1, atoi(e));  // tuning hook (bench sweeps)
     p.chunks_per_row = cfg.width ? (cfg.width + p.chunk - 1) / p.chunk : 0;
     const uint64_t npix = (uint64_t)p.rows * cfg.width;
     const uint64_t chunks = (uint64_t)p.rows * p.chunks_per_row;
@@ -427,10 +431,24 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
                     frb::frb_iterate_stream_kernel<6><<<blocks, frb::kIterateThreads, 0, st>>>(p);
                 else if (kidx == 1)
                     frb::frb_iterate_stream_kernel<7><<<blocks, frb::kIterateThreads, 0, st>>>(p);
-                else if (p.algo == FRB_ALGO_JULIA)
-                    frb::frb_iterate_sparse_kernel<6, true><<<blocks, frb::kIterateThreads, 0, st>>>(p);
-                else
-                    frb::frb_iterate_sparse_kernel<6, false><<<blocks, frb::kIterateThreads, 0, st>>>(p);
+                else {
+                    // Blocks per trip (lanes that stop early idle until the trip ends, so short pixels want short trips;
+                    // the iteration cap is the only a-priori hint): measured on C1..C4, see DESIGN.md §6.
+                    const bool julia = (p.algo == FRB_ALGO_JULIA);
+                    int nb = p.iterations >= 2048u ? 8 : (p.iterations >= 256u ? 4 : 1);
+                    if (const char *e = getenv("FRB_TUNE_NB")) nb = atoi(e);  // tuning hook (bench sweeps); 1, 4 or 8
+#define FRB_LAUNCH_SPARSE(J, NB) frb::frb_iterate_sparse_kernel<J, NB><<<blocks, frb::kIterateThreads, 0, st>>>(p)
+                    if (julia) {
+                        if (nb == 8) FRB_LAUNCH_SPARSE(true, 8);
+                        else if (nb == 4) FRB_LAUNCH_SPARSE(true, 4);
+                        else FRB_LAUNCH_SPARSE(true, 1);
+                    } else {
+                        if (nb == 8) FRB_LAUNCH_SPARSE(false, 8);
+                        else if (nb == 4) FRB_LAUNCH_SPARSE(false, 4);
+                        else FRB_LAUNCH_SPARSE(false, 1);
+                    }
+#undef FRB_LAUNCH_SPARSE
+                }
             }
             slot.launches++;
         } else {

@@ -311,209 +311,11 @@ frb_iterate_stream_kernel(const __grid_constant__ RenderParams p)
     if (lane == 0) atomicAdd(p.stats + 1, (unsigned long long)trips * (unsigned long long)(32 * kUnroll));
 }
 
-// ---------------------------------------------------------------------------------------------------------
-// K1b: persistent lane-refill iterate kernel with SPARSE escape checks (the default for sane inputs).
-//
-// Measured on B200 (scripts/issue_probe.cu, profiles/): an FP64 instruction occupies an SMSP's issue port for two
-// cycles and every other instruction for one, so the per-iteration filter of the kernel above (VIMNMX, ISETP, BRA)
-// costs 4 of 16 issue cycles.  This kernel issues NOTHING but the 6 FP64 instructions per iteration inside a block
-// of kSparseU iterations; each step's position is left in its own registers (hx[k], hy[k]: no moves, the unrolled
-// block simply rotates registers) and ONE filter per block tests the last step's squares.
-//
-// Why one test per block suffices (host-checked precondition, frb_api.cu: sparse_is_safe): with R = limit >= 8
-// and |c| <= R^2/2 - 3R for every pixel, a step with max(re^2, im^2) >= S/2 (S = R^2) is followed by
-// |z_{m}| >= |z_{m-1}|^2 - |c| >= 3R, i.e. by escaped steps only, growing doubly exponentially to +inf and then NaN
-// (inf - inf) — all of which pass the unsigned high-word filter.  So "filter fails at the end of the block"
-// proves no step of the block escaped, and "first step that passes the necessary condition" is monotone in k.
-// When the block-end filter fires, that first step is found by an integer binary search over the recorded
-// positions and the exact reference test (re^2 + im^2 > S, same products, same sum) is evaluated on it (and on the
-// next step if it was a near miss); the reference's count and final position come out bit-identical.
-// A lane whose block-end filter fired without any step escaping (S/2 <= max < S) just carries on.
-// ---------------------------------------------------------------------------------------------------------
-constexpr int kSparseU = 8;
+}  // namespace frb
 
-__device__ __forceinline__ uint32_t abs_hi(double v) { return (uint32_t)__double2hiint(v) & 0x7fffffffu; }
+#include "frb_sparse.cuh"  // K1b: the default iterate kernel (sparse escape checks, inline-PTX trip)
 
-__device__ __forceinline__ double sel_d(bool c, double a, double b) { return c ? a : b; }
-
-// A lane is idle (holds no pixel) iff left >= kIdleBit; the host only selects this kernel for iterations < 2^30.
-constexpr uint32_t kIdleBit = 0x40000000u;
-
-template <int FORM, bool JULIA>
-__global__ void __launch_bounds__(kIterateThreads, 4)
-frb_iterate_sparse_kernel(const __grid_constant__ RenderParams p)
-{
-    constexpr unsigned FULL = 0xffffffffu;
-    constexpr uint32_t U = (uint32_t)kSparseU;
-    static_assert(kSparseU == 8, "the resolve tree below is written for blocks of 8");
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned lt_mask = (1u << lane) - 1u;
-
-    const double S = p.limit_sq;
-    const uint32_t filter_hi = p.filter_hi;
-
-    Orbit o = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-    double hx[kSparseU], hy[kSparseU];
-    // A lane without a pixel runs the zero orbit (never fires the filter) with left >= kIdleBit.  Every lane starts
-    // idle, so the first pass through the service code below is a pure refill.
-    uint32_t left = kIdleBit * 2u;
-    uint32_t pix = 0;
-
-    uint32_t cur_x = 0, cur_end = 0, cur_rowpix = 0;
-    double cur_im = 0.0;
-    bool drained = false;
-    uint32_t next_chunk = 0;
-    if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
-
-    unsigned long long lane_slots = 0;  // iterations issued per lane slot (same for every lane of the warp)
-    uint32_t left_mark = left;
-    bool cand = false;
-#pragma unroll
-    for (int k = 0; k < kSparseU; ++k) hx[k] = hy[k] = 0.0;
-
-    for (;;) {
-        // ------------------------------ service (cold) ------------------------------
-        lane_slots += (unsigned long long)(left_mark - left);
-        const uint32_t iterations = p.iterations;
-        bool done = false;
-        uint32_t count = iterations;
-        if (cand) {
-            // First step k of the block whose position passes the necessary condition max(|re|,|im|) >= sqrt(S/2)
-            // (monotone in k under sparse_is_safe: a passing step is followed by escaped steps only).
-            // Binary search with the positions selected along the way; no FP64 until the single exact test.
-            const uint32_t t2 = p.filter_abs_hi;
-            const bool b2 = max(abs_hi(hx[3]), abs_hi(hy[3])) < t2;       // first pass is in 4..7
-            const double x0 = sel_d(b2, hx[4], hx[0]), x1 = sel_d(b2, hx[5], hx[1]), x2 = sel_d(b2, hx[6], hx[2]), x3 = sel_d(b2, hx[7], hx[3]);
-            const double y0 = sel_d(b2, hy[4], hy[0]), y1 = sel_d(b2, hy[5], hy[1]), y2 = sel_d(b2, hy[6], hy[2]), y3 = sel_d(b2, hy[7], hy[3]);
-            const bool b1 = max(abs_hi(x1), abs_hi(y1)) < t2;             // ... in the upper pair of that half
-            const double u0 = sel_d(b1, x2, x0), u1 = sel_d(b1, x3, x1);
-            const double v0 = sel_d(b1, y2, y0), v1 = sel_d(b1, y3, y1);
-            const bool b0 = max(abs_hi(u0), abs_hi(v0)) < t2;
-            double zx = sel_d(b0, u1, u0), zy = sel_d(b0, v1, v0);
-            uint32_t k = (b2 ? 4u : 0u) + (b1 ? 2u : 0u) + (b0 ? 1u : 0u);
-            // the reference's test on that step: same products, same sum, same compare
-            bool esc = __dadd_rn(__dmul_rn(zx, zx), __dmul_rn(zy, zy)) > S;
-            if (!esc && k < U - 1) {
-                // the passing step had S/2 <= max < S without escaping: the next one is the first that can have
-                ++k;
-                zx = hx[1]; zy = hy[1];
-                if (k == 2) { zx = hx[2]; zy = hy[2]; }
-                if (k == 3) { zx = hx[3]; zy = hy[3]; }
-                if (k == 4) { zx = hx[4]; zy = hy[4]; }
-                if (k == 5) { zx = hx[5]; zy = hy[5]; }
-                if (k == 6) { zx = hx[6]; zy = hy[6]; }
-                if (k == 7) { zx = hx[7]; zy = hy[7]; }
-                esc = __dadd_rn(__dmul_rn(zx, zx), __dmul_rn(zy, zy)) > S;
-            }
-            if (esc) {
-                done = true;
-                count = iterations - (left + U) + k;  // block's first iteration index + k
-                o.x = zx;
-                o.y = zy;
-            }
-        }
-        if (!done && left < U) {
-            // fewer than U iterations left (idle lanes have left >= kIdleBit): finish with the per-iteration test
-            done = true;
-            const uint32_t i0 = iterations - left;
-            for (uint32_t k = 0; k < left; ++k) {
-                stream_core<FORM>(o);
-                if (stream_filter(o, filter_hi) && stream_escaped(o, S)) {
-                    count = i0 + k;
-                    break;
-                }
-            }
-        }
-        if (done) {
-            // recursive() returns (next, i) on escape, (previous, iterations) otherwise
-            p.iters[pix] = count;
-            p.zfinal[pix] = make_double2(o.x, o.y);
-            left = kIdleBit * 2u;
-        }
-        unsigned need = __ballot_sync(FULL, left >= kIdleBit);
-        if (need != 0u) {
-            if (!drained) {
-                const uint32_t n = (uint32_t)__popc(need);
-                if (cur_end - cur_x >= n) {
-                    // fast path: the warp's current row segment covers every free lane
-                    if (left >= kIdleBit) {
-                        const uint32_t px = cur_x + (uint32_t)__popc(need & lt_mask);
-                        const double re0 = __ldg(p.tab_re + px);
-                        // get_recursive_pixel (calc/src/lib.rs:208-210): Mandelbrot c = start, Julia c = julia_set
-                        o.x = re0;
-                        o.y = cur_im;
-                        o.cr = JULIA ? p.julia_re : re0;
-                        o.ci = JULIA ? p.julia_im : cur_im;
-                        o.a = __dmul_rn(re0, re0);
-                        o.b = __dmul_rn(cur_im, cur_im);
-                        left = iterations;
-                        pix = cur_rowpix + px;
-                    }
-                    cur_x += n;
-                    need = 0u;
-                } else {
-                    // generic path: spans a segment boundary and/or fetches the next chunk from the queue
-                    while (need != 0u) {
-                        if (cur_x == cur_end) {
-                            const uint32_t c = __shfl_sync(FULL, next_chunk, 0);
-                            if (c >= p.total_chunks) {
-                                drained = true;
-                                break;
-                            }
-                            if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
-                            const uint32_t lr = c / p.chunks_per_row;
-                            const uint32_t seg = c - lr * p.chunks_per_row;
-                            cur_x = seg * p.chunk;
-                            cur_end = min(cur_x + p.chunk, p.width);
-                            cur_rowpix = lr * p.width;
-                            cur_im = __ldg(p.tab_im + local_row_to_y(p, lr));
-                        }
-                        const uint32_t avail = cur_end - cur_x;
-                        const uint32_t rank = __popc(need & lt_mask);
-                        if (left >= kIdleBit && rank < avail) {
-                            const uint32_t px = cur_x + rank;
-                            const double re0 = __ldg(p.tab_re + px);
-                            o.x = re0;
-                            o.y = cur_im;
-                            o.cr = JULIA ? p.julia_re : re0;
-                            o.ci = JULIA ? p.julia_im : cur_im;
-                            o.a = __dmul_rn(re0, re0);
-                            o.b = __dmul_rn(cur_im, cur_im);
-                            left = iterations;
-                            pix = cur_rowpix + px;
-                        }
-                        cur_x += min((uint32_t)__popc(need), avail);
-                        need = __ballot_sync(FULL, left >= kIdleBit);
-                    }
-                }
-            }
-            if (need != 0u) {
-                // queue drained: lanes without a pixel park on the zero orbit; the warp leaves when all are parked
-                if (need == FULL) break;
-                if (left >= kIdleBit) {
-                    o.x = o.y = o.a = o.b = o.cr = o.ci = 0.0;
-                    left = kIdleBit * 2u;
-                }
-            }
-        }
-        left_mark = left;
-
-        // ------------------------------ hot ------------------------------
-        // Per block: kSparseU x 6 FP64 instructions, then IADD, VIMNMX, 2 x ISETP, VOTE, BRA.
-        do {
-#pragma unroll
-            for (int k = 0; k < kSparseU; ++k) {
-                stream_core<FORM>(o);
-                hx[k] = o.x;
-                hy[k] = o.y;
-            }
-            left -= U;
-            cand = stream_filter(o, filter_hi);
-        } while (!__any_sync(FULL, cand || (left < U)));
-    }
-
-    if (lane == 0) atomicAdd(p.stats + 1, lane_slots * 32ull);
-}
+namespace frb {
 
 // ---------------------------------------------------------------------------------------------------------
 // K1s: cross-check kernel — one thread per pixel, reference order as written, no queue, no refill.
