@@ -72,6 +72,8 @@ struct DeviceCtx {
     int sm_count = 0;
     int iter_blocks_per_sm[3] = {0, 0, 0};  // dense FORM 6, dense FORM 7, sparse FORM 6
     cudaStream_t stream = nullptr;       // the library's own stream for this device
+    cudaStream_t aux[2] = {nullptr, nullptr};  // slab streams of the host-output path
+    cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr}, ev_slab[16] = {};
     cudaEvent_t ev_guard = nullptr;      // completion of the last render that used the shared raw buffers
     cudaStream_t last_stream = nullptr;
     bool have_guard = false;
@@ -121,6 +123,12 @@ int ctx_init(DeviceCtx *c, int dev)
     c->sm_count = prop.multiProcessorCount;
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&c->ev_guard, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    for (auto &e : c->ev_slab) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (int i = 0; i < 2; ++i) {
+        CU(cudaStreamCreateWithFlags(&c->aux[i], cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming));
+    }
     CU(cudaMalloc(&c->queue, 256));
     CU(cudaMalloc(&c->stats, 256));
     for (auto &s : c->slots) {
@@ -162,6 +170,13 @@ void ctx_destroy(DeviceCtx *c)
             if (s.host) cudaFreeHost(s.host);
         }
         if (c->ev_guard) cudaEventDestroy(c->ev_guard);
+        if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+        for (auto &e : c->ev_slab)
+            if (e) cudaEventDestroy(e);
+        for (int i = 0; i < 2; ++i) {
+            if (c->ev_join[i]) cudaEventDestroy(c->ev_join[i]);
+            if (c->aux[i]) cudaStreamDestroy(c->aux[i]);
+        }
         if (c->stream) cudaStreamDestroy(c->stream);
     }
     delete c;
@@ -395,10 +410,61 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
 }
 
 // Enqueues tables -> iterate -> shade (if format != 0) on `st`.  Caller holds c.mu and has set the device.
-int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **slot_out)
+// Launches the iteration kernel chosen by plan.variant for the chunks [p.chunk_begin, p.chunk_begin + p.total_chunks).
+int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaStream_t st)
 {
-    RenderParams &p = plan.p;
-    p.out = dev_out;
+    if (plan.variant == FRB_KERNEL_SIMPLE) {
+        dim3 grid(p.rows, (p.width + 255) / 256);
+        frb::frb_iterate_simple_kernel<<<grid, 256, 0, st>>>(p);
+        return FRB_OK;
+    }
+    const int kidx = (plan.variant == FRB_KERNEL_STREAM7) ? 1 : (plan.variant == FRB_KERNEL_DENSE6 ? 0 : 2);
+    const uint32_t warps_per_block = frb::kIterateThreads / 32;
+    uint32_t blocks = (uint32_t)(c.sm_count * c.iter_blocks_per_sm[kidx]);
+    const uint32_t needed = (p.total_chunks + warps_per_block - 1) / warps_per_block;
+    blocks = std::max(1u, std::min(blocks, needed));
+    if (kidx == 0) {
+        frb::frb_iterate_stream_kernel<6><<<blocks, frb::kIterateThreads, 0, st>>>(p);
+    } else if (kidx == 1) {
+        frb::frb_iterate_stream_kernel<7><<<blocks, frb::kIterateThreads, 0, st>>>(p);
+    } else {
+        // Blocks per trip (lanes that stop early idle until the trip ends, so short pixels want short trips; the
+        // iteration cap is the only a-priori hint): measured on C1..C4, profiles/r1_tuning_sweeps.txt.
+        const bool julia = (p.algo == FRB_ALGO_JULIA);
+        int nb = p.iterations >= 2048u ? 8 : (p.iterations >= 256u ? 4 : 1);
+        if (const char *e = getenv("FRB_TUNE_NB")) nb = atoi(e);  // tuning hook (bench sweeps); 1, 4 or 8
+#define FRB_LAUNCH_SPARSE(J, NB) frb::frb_iterate_sparse_kernel<J, NB><<<blocks, frb::kIterateThreads, 0, st>>>(p)
+        if (julia) {
+            if (nb == 8) FRB_LAUNCH_SPARSE(true, 8);
+            else if (nb == 4) FRB_LAUNCH_SPARSE(true, 4);
+            else FRB_LAUNCH_SPARSE(true, 1);
+        } else {
+            if (nb == 8) FRB_LAUNCH_SPARSE(false, 8);
+            else if (nb == 4) FRB_LAUNCH_SPARSE(false, 4);
+            else FRB_LAUNCH_SPARSE(false, 1);
+        }
+#undef FRB_LAUNCH_SPARSE
+    }
+    return FRB_OK;
+}
+
+// Shade (or, with format 0, only sum the iterations of) the pixels the pointers of `p` address: p.rows x p.width.
+void launch_shade(DeviceCtx &c, const RenderParams &p, cudaStream_t st)
+{
+    const uint64_t npix = (uint64_t)p.rows * p.width;
+    if (p.format != 0) {
+        const uint64_t cta_px = (uint64_t)frb::kShadeThreads * frb::kShadePxPerThread;
+        const uint64_t nblocks = (npix + cta_px - 1) / cta_px;
+        const uint32_t grid = (uint32_t)std::min<uint64_t>(nblocks, (uint64_t)c.sm_count * 32);
+        frb::frb_shade_kernel<<<grid, frb::kShadeThreads, 0, st>>>(p);
+    } else {
+        const uint32_t grid = (uint32_t)std::min<uint64_t>((npix + 255) / 256, (uint64_t)c.sm_count * 16);
+        frb::frb_sum_iterations_kernel<<<grid, 256, 0, st>>>(p);
+    }
+}
+
+Slot &take_slot(DeviceCtx &c, const Plan &plan)
+{
     Slot &slot = c.slots[c.next_slot];
     c.next_slot = (c.next_slot + 1) % kSlots;
     slot.pixels = plan.npix;
@@ -407,6 +473,15 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
     slot.shaded = false;
     slot.host->iterations = 0;
     slot.host->lane_iterations = 0;
+    return slot;
+}
+
+// Enqueues tables -> iterate -> shade (if format != 0) on `st`.  Caller holds c.mu and has set the device.
+int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **slot_out)
+{
+    RenderParams &p = plan.p;
+    p.out = dev_out;
+    Slot &slot = take_slot(c, plan);
     *slot_out = &slot;
 
     // the raw buffers (tables, counts, final z, queue) are shared by all renders of this device: order streams
@@ -418,38 +493,7 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
         frb::frb_coord_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
         slot.launches++;
         if (p.algo != FRB_ALGO_BARNSLEY_FERN) {
-            if (plan.variant == FRB_KERNEL_SIMPLE) {
-                dim3 grid(p.rows, (p.width + 255) / 256);
-                frb::frb_iterate_simple_kernel<<<grid, 256, 0, st>>>(p);
-            } else {
-                const int kidx = (plan.variant == FRB_KERNEL_STREAM7) ? 1 : (plan.variant == FRB_KERNEL_DENSE6 ? 0 : 2);
-                const uint32_t warps_per_block = frb::kIterateThreads / 32;
-                uint32_t blocks = (uint32_t)(c.sm_count * c.iter_blocks_per_sm[kidx]);
-                const uint32_t needed = (p.total_chunks + warps_per_block - 1) / warps_per_block;
-                blocks = std::max(1u, std::min(blocks, needed));
-                if (kidx == 0)
-                    frb::frb_iterate_stream_kernel<6><<<blocks, frb::kIterateThreads, 0, st>>>(p);
-                else if (kidx == 1)
-                    frb::frb_iterate_stream_kernel<7><<<blocks, frb::kIterateThreads, 0, st>>>(p);
-                else {
-                    // Blocks per trip (lanes that stop early idle until the trip ends, so short pixels want short trips;
-                    // the iteration cap is the only a-priori hint): measured on C1..C4, see DESIGN.md §6.
-                    const bool julia = (p.algo == FRB_ALGO_JULIA);
-                    int nb = p.iterations >= 2048u ? 8 : (p.iterations >= 256u ? 4 : 1);
-                    if (const char *e = getenv("FRB_TUNE_NB")) nb = atoi(e);  // tuning hook (bench sweeps); 1, 4 or 8
-#define FRB_LAUNCH_SPARSE(J, NB) frb::frb_iterate_sparse_kernel<J, NB><<<blocks, frb::kIterateThreads, 0, st>>>(p)
-                    if (julia) {
-                        if (nb == 8) FRB_LAUNCH_SPARSE(true, 8);
-                        else if (nb == 4) FRB_LAUNCH_SPARSE(true, 4);
-                        else FRB_LAUNCH_SPARSE(true, 1);
-                    } else {
-                        if (nb == 8) FRB_LAUNCH_SPARSE(false, 8);
-                        else if (nb == 4) FRB_LAUNCH_SPARSE(false, 4);
-                        else FRB_LAUNCH_SPARSE(false, 1);
-                    }
-#undef FRB_LAUNCH_SPARSE
-                }
-            }
+            if (int rc = launch_iterate(c, plan, p, st)) return rc;
             slot.launches++;
         } else {
             // get_recursive_pixel returns BLACK without iterating (calc/src/lib.rs:211); keep the raw outputs defined
@@ -458,21 +502,73 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
         }
     }
     CU(cudaEventRecord(slot.ev_iter, st));
-    if (plan.npix > 0 && p.format != 0) {
-        const uint64_t cta_px = (uint64_t)frb::kShadeThreads * frb::kShadePxPerThread;
-        const uint64_t nblocks = (plan.npix + cta_px - 1) / cta_px;
-        const uint32_t grid = (uint32_t)std::min<uint64_t>(nblocks, (uint64_t)c.sm_count * 32);
-        frb::frb_shade_kernel<<<grid, frb::kShadeThreads, 0, st>>>(p);
+    if (plan.npix > 0) {
+        launch_shade(c, p, st);
         slot.launches++;
-        slot.shaded = true;
-    }
-    else if (plan.npix > 0) {
-        const uint32_t grid = (uint32_t)std::min<uint64_t>((plan.npix + 255) / 256, (uint64_t)c.sm_count * 16);
-        frb::frb_sum_iterations_kernel<<<grid, 256, 0, st>>>(p);
-        slot.launches++;
+        slot.shaded = (p.format != 0);
     }
     CU(cudaEventRecord(slot.ev_shade, st));
     if (plan.npix > 0) CU(cudaMemcpyAsync(slot.host, c.stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, st));
+    CU(cudaGetLastError());
+    return FRB_OK;
+}
+
+// Host-output path for large frames: the shard is cut into row slabs, each iterated + shaded + copied out on one of two
+// auxiliary streams.  The iterate kernels are persistent full-GPU grids, so slab s+1's CTAs start as slab s's CTAs
+// drain (its tail is filled) and slab s's device->host copy runs under slab s+1's iterations.  Nothing waits on
+// anything but stream order and events.  `host_out` should be pinned for the copies to be asynchronous.
+int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot **slot_out)
+{
+    RenderParams &p = plan.p;
+    p.out = c.out;
+    Slot &slot = take_slot(c, plan);
+    *slot_out = &slot;
+    cudaStream_t st = c.stream;
+    if (c.have_guard && c.last_stream != st) CU(cudaStreamWaitEvent(st, c.ev_guard, 0));
+    CU(cudaEventRecord(slot.ev_start, st));
+    const uint32_t n = std::max(p.width, p.height);
+    frb::frb_coord_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
+    slot.launches++;
+    CU(cudaEventRecord(c.ev_fork, st));
+    const uint32_t rows_per = ((p.rows + nslabs - 1) / nslabs + 15u) & ~15u;  // multiples of 16 rows keep 16-byte alignment
+    // measured on C2 (profiles/r1_tuning_sweeps.txt): overlapped slabs 5.555 ms, pipelined 5.58-5.78 ms, unsliced 5.60 ms
+    const bool pipeline = getenv("FRB_TUNE_SLABMODE") ? atoi(getenv("FRB_TUNE_SLABMODE")) == 2 : false;
+    int s = 0;
+    for (uint32_t r0 = 0; r0 < p.rows; r0 += rows_per, ++s) {
+        // pipeline: kernels of all slabs in order on aux[0], copies on aux[1] behind per-slab events.
+        // otherwise: slabs alternate between the two streams and their kernels overlap freely.
+        cudaStream_t ks = pipeline ? c.aux[0] : c.aux[s & 1];
+        cudaStream_t cs = pipeline ? c.aux[1] : ks;
+        if (s < 2) CU(cudaStreamWaitEvent(c.aux[s & 1], c.ev_fork, 0));
+        const uint32_t r1 = std::min(p.rows, r0 + rows_per);
+        RenderParams it = p;  // iterate: global pixel indexing, its own chunk range and queue counter
+        it.chunk_begin = r0 * p.chunks_per_row;
+        it.total_chunks = (r1 - r0) * p.chunks_per_row;
+        it.queue = c.queue + (s % 16);
+        if (int rc = launch_iterate(c, plan, it, ks)) return rc;
+        RenderParams sh = p;  // shade: the slab's pixels through offset pointers
+        const size_t pix0 = (size_t)r0 * p.width;
+        sh.rows = r1 - r0;
+        sh.iters = p.iters + pix0;
+        sh.zfinal = p.zfinal + pix0;
+        sh.out = p.out + pix0 * p.format;
+        launch_shade(c, sh, ks);
+        slot.launches += 2;
+        if (pipeline) {
+            CU(cudaEventRecord(c.ev_slab[s % 16], ks));
+            CU(cudaStreamWaitEvent(cs, c.ev_slab[s % 16], 0));
+        }
+        const size_t bytes = (size_t)(r1 - r0) * p.width * p.format;
+        CU(cudaMemcpyAsync(host_out + pix0 * p.format, sh.out, bytes, cudaMemcpyDeviceToHost, cs));
+    }
+    for (int i = 0; i < 2; ++i) {
+        CU(cudaEventRecord(c.ev_join[i], c.aux[i]));
+        CU(cudaStreamWaitEvent(st, c.ev_join[i], 0));
+    }
+    slot.shaded = true;
+    CU(cudaEventRecord(slot.ev_iter, st));
+    CU(cudaEventRecord(slot.ev_shade, st));
+    CU(cudaMemcpyAsync(slot.host, c.stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, st));
     CU(cudaGetLastError());
     return FRB_OK;
 }
@@ -532,11 +628,20 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
         if (int rc = ensure(c->out, c->out_cap, plan.out_bytes + 64)) return rc;
     }
     Slot *slot = nullptr;
-    if (int rc = enqueue(*c, plan, c->out, c->stream, &slot)) return rc;
-    if (plan.npix > 0) {
-        if (format != 0) CU(cudaMemcpyAsync(host_out, c->out, plan.out_bytes, cudaMemcpyDeviceToHost, c->stream));
-        if (host_iters) CU(cudaMemcpyAsync(host_iters, c->iters, plan.npix * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
-        if (host_z) CU(cudaMemcpyAsync(host_z, c->zfinal, plan.npix * sizeof(double2), cudaMemcpyDeviceToHost, c->stream));
+    // Large RGB/RGBA frames go out in row slabs so that the device->host copy hides under the iterations.
+    const bool sliced = format != 0 && !host_iters && !host_z && plan.variant != FRB_KERNEL_SIMPLE &&
+                        cfg.algo != FRB_ALGO_BARNSLEY_FERN && plan.npix >= (4u << 20) && plan.p.rows >= 256u &&
+                        !getenv("FRB_TUNE_NOSLAB");
+    if (sliced) {
+        const int nslabs = getenv("FRB_TUNE_SLABS") ? std::min(16, std::max(1, atoi(getenv("FRB_TUNE_SLABS")))) : 4;
+        if (int rc = enqueue_sliced(*c, plan, host_out, nslabs, &slot)) return rc;
+    } else {
+        if (int rc = enqueue(*c, plan, c->out, c->stream, &slot)) return rc;
+        if (plan.npix > 0) {
+            if (format != 0) CU(cudaMemcpyAsync(host_out, c->out, plan.out_bytes, cudaMemcpyDeviceToHost, c->stream));
+            if (host_iters) CU(cudaMemcpyAsync(host_iters, c->iters, plan.npix * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+            if (host_z) CU(cudaMemcpyAsync(host_z, c->zfinal, plan.npix * sizeof(double2), cudaMemcpyDeviceToHost, c->stream));
+        }
     }
     if (int rc = finish_enqueue(*c, *slot, c->stream)) return rc;
     CU(cudaStreamSynchronize(c->stream));

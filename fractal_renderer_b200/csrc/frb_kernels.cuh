@@ -52,6 +52,8 @@ struct RenderParams {
     uint32_t secondary;
     uint32_t format;       // 3 = RGB24, 4 = RGBA32
     uint32_t filter_abs_hi; // high word of sqrt(S/2), minus 1: max(|re|,|im|) >= this is necessary for re^2+im^2 > S/2
+    uint32_t chunk_begin;   // first chunk of this launch (row slabs of one shard are separate launches); 0 normally
+    uint32_t pad1;
     // buffers
     double *tab_re;              // [width]   re0(x)
     double *tab_im;              // [height]  im0(y), indexed by IMAGE row
@@ -78,8 +80,8 @@ __device__ __forceinline__ uint32_t local_row_to_y(const RenderParams &p, uint32
 __global__ void frb_coord_tables_kernel(const __grid_constant__ RenderParams p)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < 16) p.queue[t] = 0u;  // one counter per row slab (frb_api.cu: enqueue_sliced)
     if (t == 0) {
-        *p.queue = 0u;
         p.stats[0] = 0ull;
         p.stats[1] = 0ull;
     }
@@ -227,8 +229,9 @@ frb_iterate_stream_kernel(const __grid_constant__ RenderParams p)
                         break;
                     }
                     if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
-                    const uint32_t lr = c / p.chunks_per_row;
-                    const uint32_t seg = c - lr * p.chunks_per_row;
+                    const uint32_t cg = c + p.chunk_begin;
+                    const uint32_t lr = cg / p.chunks_per_row;
+                    const uint32_t seg = cg - lr * p.chunks_per_row;
                     cur_x = seg * p.chunk;
                     cur_end = min(cur_x + p.chunk, p.width);
                     cur_rowpix = lr * p.width;

@@ -197,8 +197,9 @@ frb_iterate_sparse_kernel(const __grid_constant__ RenderParams p)
                                 break;
                             }
                             if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
-                            const uint32_t lr = c / p.chunks_per_row;
-                            const uint32_t seg = c - lr * p.chunks_per_row;
+                            const uint32_t cg = c + p.chunk_begin;
+                            const uint32_t lr = cg / p.chunks_per_row;
+                            const uint32_t seg = cg - lr * p.chunks_per_row;
                             cur_x = seg * p.chunk;
                             cur_end = min(cur_x + p.chunk, p.width);
                             cur_rowpix = lr * p.width;
