@@ -74,21 +74,26 @@ struct DeviceCtx {
     cudaStream_t stream = nullptr;       // the library's own stream for this device
     cudaStream_t aux[2] = {nullptr, nullptr};  // slab streams of the host-output path
     cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr}, ev_slab[16] = {};
-    cudaEvent_t ev_guard = nullptr;      // completion of the last render that used the shared raw buffers
-    cudaStream_t last_stream = nullptr;
-    bool have_guard = false;
+    // Two sets of per-render device buffers: blocking and async renders use set 0; frb_render_frames alternates sets
+    // (and streams) so that frame k+1's iterations fill the tail of frame k and hide its copy-out.
+    struct BufSet {
+        cudaEvent_t ev_guard = nullptr;  // completion of the last render that used this set
+        cudaStream_t last_stream = nullptr;
+        bool have_guard = false;
+        double *tab = nullptr;           // grow-only
+        size_t tab_cap = 0;              // doubles
+        uint32_t *iters = nullptr;
+        size_t iters_cap = 0;            // elements
+        double2 *zfinal = nullptr;
+        size_t z_cap = 0;
+        uint8_t *out = nullptr;
+        size_t out_cap = 0;              // bytes
+        unsigned int *queue = nullptr;   // 16 chunk counters
+        unsigned long long *stats = nullptr;
+    } sets[2];
+    int cur_set = 0;
+    BufSet &b() { return sets[cur_set]; }
     std::mutex mu;
-    // grow-only device buffers
-    double *tab = nullptr;
-    size_t tab_cap = 0;  // doubles
-    uint32_t *iters = nullptr;
-    size_t iters_cap = 0;  // elements
-    double2 *zfinal = nullptr;
-    size_t z_cap = 0;
-    uint8_t *out = nullptr;
-    size_t out_cap = 0;  // bytes
-    unsigned int *queue = nullptr;
-    unsigned long long *stats = nullptr;
     Slot slots[kSlots];
     uint32_t next_slot = 0;
 };
@@ -122,15 +127,17 @@ int ctx_init(DeviceCtx *c, int dev)
         return fail(FRB_ERR_NO_DEVICE, "device %d is sm_%d%d; this library carries sm_100a code only", dev, prop.major, prop.minor);
     c->sm_count = prop.multiProcessorCount;
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    CU(cudaEventCreateWithFlags(&c->ev_guard, cudaEventDisableTiming));
+    for (auto &bs : c->sets) {
+        CU(cudaEventCreateWithFlags(&bs.ev_guard, cudaEventDisableTiming));
+        CU(cudaMalloc(&bs.queue, 256));
+        CU(cudaMalloc(&bs.stats, 256));
+    }
     CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     for (auto &e : c->ev_slab) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (int i = 0; i < 2; ++i) {
         CU(cudaStreamCreateWithFlags(&c->aux[i], cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming));
     }
-    CU(cudaMalloc(&c->queue, 256));
-    CU(cudaMalloc(&c->stats, 256));
     for (auto &s : c->slots) {
         CU(cudaEventCreate(&s.ev_start));
         CU(cudaEventCreate(&s.ev_iter));
@@ -156,12 +163,15 @@ void ctx_destroy(DeviceCtx *c)
     if (!c) return;
     if (c->dev >= 0 && cudaSetDevice(c->dev) == cudaSuccess) {
         cudaDeviceSynchronize();
-        cudaFree(c->tab);
-        cudaFree(c->iters);
-        cudaFree(c->zfinal);
-        cudaFree(c->out);
-        cudaFree(c->queue);
-        cudaFree(c->stats);
+        for (auto &bs : c->sets) {
+            cudaFree(bs.tab);
+            cudaFree(bs.iters);
+            cudaFree(bs.zfinal);
+            cudaFree(bs.out);
+            cudaFree(bs.queue);
+            cudaFree(bs.stats);
+            if (bs.ev_guard) cudaEventDestroy(bs.ev_guard);
+        }
         for (auto &s : c->slots) {
             if (s.ev_start) cudaEventDestroy(s.ev_start);
             if (s.ev_iter) cudaEventDestroy(s.ev_iter);
@@ -169,7 +179,6 @@ void ctx_destroy(DeviceCtx *c)
             if (s.ev_end) cudaEventDestroy(s.ev_end);
             if (s.host) cudaFreeHost(s.host);
         }
-        if (c->ev_guard) cudaEventDestroy(c->ev_guard);
         if (c->ev_fork) cudaEventDestroy(c->ev_fork);
         for (auto &e : c->ev_slab)
             if (e) cudaEventDestroy(e);
@@ -397,15 +406,15 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     if (v == FRB_KERNEL_DENSE6 && !form6_is_exact(cfg)) v = FRB_KERNEL_STREAM7;
     plan->variant = v;
 
-    if (int rc = ensure(c.tab, c.tab_cap, (size_t)cfg.width + cfg.height + 2)) return rc;
-    if (int rc = ensure(c.iters, c.iters_cap, (size_t)npix + 4)) return rc;
-    if (int rc = ensure(c.zfinal, c.z_cap, (size_t)npix + 4)) return rc;
-    p.tab_re = c.tab;
-    p.tab_im = c.tab + cfg.width;
-    p.iters = c.iters;
-    p.zfinal = c.zfinal;
-    p.queue = c.queue;
-    p.stats = c.stats;
+    if (int rc = ensure(c.b().tab, c.b().tab_cap, (size_t)cfg.width + cfg.height + 2)) return rc;
+    if (int rc = ensure(c.b().iters, c.b().iters_cap, (size_t)npix + 4)) return rc;
+    if (int rc = ensure(c.b().zfinal, c.b().z_cap, (size_t)npix + 4)) return rc;
+    p.tab_re = c.b().tab;
+    p.tab_im = c.b().tab + cfg.width;
+    p.iters = c.b().iters;
+    p.zfinal = c.b().zfinal;
+    p.queue = c.b().queue;
+    p.stats = c.b().stats;
     return FRB_OK;
 }
 
@@ -485,7 +494,7 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
     *slot_out = &slot;
 
     // the raw buffers (tables, counts, final z, queue) are shared by all renders of this device: order streams
-    if (c.have_guard && c.last_stream != st) CU(cudaStreamWaitEvent(st, c.ev_guard, 0));
+    if (c.b().have_guard && c.b().last_stream != st) CU(cudaStreamWaitEvent(st, c.b().ev_guard, 0));
 
     CU(cudaEventRecord(slot.ev_start, st));
     if (plan.npix > 0) {
@@ -508,7 +517,7 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
         slot.shaded = (p.format != 0);
     }
     CU(cudaEventRecord(slot.ev_shade, st));
-    if (plan.npix > 0) CU(cudaMemcpyAsync(slot.host, c.stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, st));
+    if (plan.npix > 0) CU(cudaMemcpyAsync(slot.host, c.b().stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, st));
     CU(cudaGetLastError());
     return FRB_OK;
 }
@@ -520,11 +529,11 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
 int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot **slot_out)
 {
     RenderParams &p = plan.p;
-    p.out = c.out;
+    p.out = c.b().out;
     Slot &slot = take_slot(c, plan);
     *slot_out = &slot;
     cudaStream_t st = c.stream;
-    if (c.have_guard && c.last_stream != st) CU(cudaStreamWaitEvent(st, c.ev_guard, 0));
+    if (c.b().have_guard && c.b().last_stream != st) CU(cudaStreamWaitEvent(st, c.b().ev_guard, 0));
     CU(cudaEventRecord(slot.ev_start, st));
     const uint32_t n = std::max(p.width, p.height);
     frb::frb_coord_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
@@ -544,7 +553,7 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
         RenderParams it = p;  // iterate: global pixel indexing, its own chunk range and queue counter
         it.chunk_begin = r0 * p.chunks_per_row;
         it.total_chunks = (r1 - r0) * p.chunks_per_row;
-        it.queue = c.queue + (s % 16);
+        it.queue = c.b().queue + (s % 16);
         if (int rc = launch_iterate(c, plan, it, ks)) return rc;
         RenderParams sh = p;  // shade: the slab's pixels through offset pointers
         const size_t pix0 = (size_t)r0 * p.width;
@@ -568,7 +577,7 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
     slot.shaded = true;
     CU(cudaEventRecord(slot.ev_iter, st));
     CU(cudaEventRecord(slot.ev_shade, st));
-    CU(cudaMemcpyAsync(slot.host, c.stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(slot.host, c.b().stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, st));
     CU(cudaGetLastError());
     return FRB_OK;
 }
@@ -576,9 +585,9 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
 int finish_enqueue(DeviceCtx &c, Slot &slot, cudaStream_t st)
 {
     CU(cudaEventRecord(slot.ev_end, st));
-    CU(cudaEventRecord(c.ev_guard, st));
-    c.have_guard = true;
-    c.last_stream = st;
+    CU(cudaEventRecord(c.b().ev_guard, st));
+    c.b().have_guard = true;
+    c.b().last_stream = st;
     return FRB_OK;
 }
 
@@ -625,7 +634,7 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
     if (format != 0) {
         if (out_len < plan.out_bytes) return fail(FRB_ERR_INVALID, "output buffer too small: %zu < %zu bytes", out_len, plan.out_bytes);
         if (plan.out_bytes && !host_out) return fail(FRB_ERR_INVALID, "null output buffer");
-        if (int rc = ensure(c->out, c->out_cap, plan.out_bytes + 64)) return rc;
+        if (int rc = ensure(c->b().out, c->b().out_cap, plan.out_bytes + 64)) return rc;
     }
     Slot *slot = nullptr;
     // Large RGB/RGBA frames go out in row slabs so that the device->host copy hides under the iterations.
@@ -636,11 +645,11 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
         const int nslabs = getenv("FRB_TUNE_SLABS") ? std::min(16, std::max(1, atoi(getenv("FRB_TUNE_SLABS")))) : 4;
         if (int rc = enqueue_sliced(*c, plan, host_out, nslabs, &slot)) return rc;
     } else {
-        if (int rc = enqueue(*c, plan, c->out, c->stream, &slot)) return rc;
+        if (int rc = enqueue(*c, plan, c->b().out, c->stream, &slot)) return rc;
         if (plan.npix > 0) {
-            if (format != 0) CU(cudaMemcpyAsync(host_out, c->out, plan.out_bytes, cudaMemcpyDeviceToHost, c->stream));
-            if (host_iters) CU(cudaMemcpyAsync(host_iters, c->iters, plan.npix * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
-            if (host_z) CU(cudaMemcpyAsync(host_z, c->zfinal, plan.npix * sizeof(double2), cudaMemcpyDeviceToHost, c->stream));
+            if (format != 0) CU(cudaMemcpyAsync(host_out, c->b().out, plan.out_bytes, cudaMemcpyDeviceToHost, c->stream));
+            if (host_iters) CU(cudaMemcpyAsync(host_iters, c->b().iters, plan.npix * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+            if (host_z) CU(cudaMemcpyAsync(host_z, c->b().zfinal, plan.npix * sizeof(double2), cudaMemcpyDeviceToHost, c->stream));
         }
     }
     if (int rc = finish_enqueue(*c, *slot, c->stream)) return rc;
@@ -814,8 +823,8 @@ int frb_render(const FrbConfig *cfg, uint8_t *out, size_t out_len, uint32_t form
         CU(cudaSetDevice(c.dev));
         FrbShard sh = {g, G, kDefaultBandRows, 0u};
         if (int rc = make_plan(c, *cfg, sh, format, &parts[g].plan)) return rc;
-        if (int rc = ensure(c.out, c.out_cap, parts[g].plan.out_bytes + 64)) return rc;
-        if (int rc = enqueue(c, parts[g].plan, c.out, c.stream, &parts[g].slot)) return rc;
+        if (int rc = ensure(c.b().out, c.b().out_cap, parts[g].plan.out_bytes + 64)) return rc;
+        if (int rc = enqueue(c, parts[g].plan, c.b().out, c.stream, &parts[g].slot)) return rc;
         const uint32_t rows = parts[g].plan.p.rows;
         if (rows > 0) {
             // full bands: one strided copy; the (possibly partial) last band separately
@@ -823,10 +832,10 @@ int frb_render(const FrbConfig *cfg, uint8_t *out, size_t out_len, uint32_t form
             const uint32_t full = rows / kDefaultBandRows;
             uint8_t *dst0 = out + (size_t)g * band_bytes;
             if (full > 0)
-                CU(cudaMemcpy2DAsync(dst0, (size_t)G * band_bytes, c.out, band_bytes, band_bytes, full, cudaMemcpyDeviceToHost, c.stream));
+                CU(cudaMemcpy2DAsync(dst0, (size_t)G * band_bytes, c.b().out, band_bytes, band_bytes, full, cudaMemcpyDeviceToHost, c.stream));
             const uint32_t rest = rows - full * kDefaultBandRows;
             if (rest > 0)
-                CU(cudaMemcpyAsync(dst0 + (size_t)full * G * band_bytes, c.out + (size_t)full * band_bytes, (size_t)rest * row_bytes,
+                CU(cudaMemcpyAsync(dst0 + (size_t)full * G * band_bytes, c.b().out + (size_t)full * band_bytes, (size_t)rest * row_bytes,
                                    cudaMemcpyDeviceToHost, c.stream));
         }
         if (int rc = finish_enqueue(c, *parts[g].slot, c.stream)) return rc;
@@ -905,19 +914,28 @@ int frb_render_frames(const FrbConfig *cfgs, uint32_t n, uint8_t *out, size_t ou
         pending[g].clear();
         return FRB_OK;
     };
+    std::vector<uint32_t> nth(G, 0);  // frames issued per device
     for (uint32_t k = 0; k < n; ++k) {
         const uint32_t g = k % G;
         DeviceCtx &c = *ctx[g];
         if (pending[g].size() >= (size_t)kSlots - 1)
             if (int rc = drain(g)) return rc;
         CU(cudaSetDevice(c.dev));
+        // alternate buffer set and stream: frame j+1's persistent CTAs start as frame j's drain, and frame j's
+        // shade + copy-out run in frame j+1's shadow
+        const int alt = (int)(nth[g]++ & 1u);
+        c.cur_set = alt;
+        cudaStream_t st = c.aux[alt];
         Plan plan;
-        if (int rc = make_plan(c, cfgs[k], whole_frame(), format, &plan)) return rc;
-        if (int rc = ensure(c.out, c.out_cap, plan.out_bytes + 64)) return rc;
+        int rc = make_plan(c, cfgs[k], whole_frame(), format, &plan);
+        if (!rc) rc = ensure(c.b().out, c.b().out_cap, plan.out_bytes + 64);
         Slot *slot = nullptr;
-        if (int rc = enqueue(c, plan, c.out, c.stream, &slot)) return rc;
-        if (plan.out_bytes) CU(cudaMemcpyAsync(out + offset[k], c.out, plan.out_bytes, cudaMemcpyDeviceToHost, c.stream));
-        if (int rc = finish_enqueue(c, *slot, c.stream)) return rc;
+        if (!rc) rc = enqueue(c, plan, c.b().out, st, &slot);
+        if (!rc && plan.out_bytes && cudaMemcpyAsync(out + offset[k], c.b().out, plan.out_bytes, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+            rc = fail(FRB_ERR_CUDA, "cudaMemcpyAsync (frame %u) failed: %s", k, cudaGetErrorString(cudaGetLastError()));
+        if (!rc) rc = finish_enqueue(c, *slot, st);
+        c.cur_set = 0;
+        if (rc) return rc;
         pending[g].push_back(slot);
     }
     for (uint32_t g = 0; g < G; ++g)
