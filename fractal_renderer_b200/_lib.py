@@ -50,6 +50,12 @@ EXPORTS = (
     "frb_last_error",
     "frb_last_stats",
     "frb_measure_fp64_peak",
+    "frb_server_create",
+    "frb_server_destroy",
+    "frb_server_request",
+    "frb_server_poll",
+    "frb_server_stats",
+    "frb_server_last_error",
 )
 
 
@@ -87,6 +93,15 @@ class FrbFp64Peak(ctypes.Structure):
         ("sm_count", ctypes.c_uint32),
         ("reserved", ctypes.c_uint32),
     ]
+
+
+class FrbServerStats(ctypes.Structure):
+    _fields_ = [("requests", ctypes.c_uint64), ("coalesced", ctypes.c_uint64), ("frames_rendered", ctypes.c_uint64),
+                ("working", ctypes.c_uint32), ("try_redraw", ctypes.c_uint32)]
+
+
+SERVER_RENDER_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.POINTER(FrbConfig), ctypes.POINTER(ctypes.c_uint8), ctypes.c_size_t,
+                                    ctypes.c_void_p)
 
 
 class FrbError(RuntimeError):
@@ -145,6 +160,19 @@ def load() -> ctypes.CDLL:
     L.frb_last_stats.argtypes = [P(FrbStats)]
     L.frb_measure_fp64_peak.restype = ctypes.c_int
     L.frb_measure_fp64_peak.argtypes = [ctypes.c_int, P(FrbFp64Peak)]
+    L.frb_server_create.restype = ctypes.c_void_p
+    L.frb_server_create.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    L.frb_server_destroy.restype = None
+    L.frb_server_destroy.argtypes = [ctypes.c_void_p]
+    L.frb_server_request.restype = ctypes.c_int
+    L.frb_server_request.argtypes = [ctypes.c_void_p, P(FrbConfig)]
+    L.frb_server_poll.restype = ctypes.c_int
+    L.frb_server_poll.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, P(ctypes.c_uint32), P(ctypes.c_uint32),
+                                  ctypes.c_int]
+    L.frb_server_stats.restype = ctypes.c_int
+    L.frb_server_stats.argtypes = [ctypes.c_void_p, P(FrbServerStats)]
+    L.frb_server_last_error.restype = ctypes.c_char_p
+    L.frb_server_last_error.argtypes = [ctypes.c_void_p]
     if L.frb_abi_version() != 1:
         raise FrbError(FRB_ERR_INVALID, f"ABI version mismatch: library {L.frb_abi_version()}, binding 1")
     _lib = L

@@ -183,6 +183,34 @@ int frb_sync_stats(FrbStats *stats);
  * library keeps the 32 most recent), so a caller can keep the next frame enqueued while harvesting. */
 int frb_async_stats(uint32_t back, FrbStats *stats);
 
+/* ---- headless frame server (the reference GUI's render thread without the window) -------- */
+
+/* Mirrors src/gui.rs:37-48 (request_redraw, latest-wins coalescing through working/try_redraw), :56-82 (render thread:
+ * config -> get_image -> RGBA8 frame -> shared slot) and :110-117 (the UI takes the frame and re-requests).  The GL
+ * texture upload is left out (no graphics stack); the caller receives the RGBA frame. */
+typedef struct FrbServer FrbServer;
+/* Renderer hook: fill `rgba` (width*height*4 bytes) for `cfg`, return FRB_OK or an error.  NULL = frb_render(RGBA32). */
+typedef int (*FrbServerRenderFn)(const FrbConfig *cfg, uint8_t *rgba, size_t len, void *user);
+typedef struct FrbServerStats {
+    uint64_t requests;        /* frb_server_request calls + re-requests issued on poll */
+    uint64_t coalesced;       /* requests absorbed because a render was in flight (try_redraw) */
+    uint64_t frames_rendered;
+    uint32_t working;
+    uint32_t try_redraw;
+} FrbServerStats;
+
+FrbServer *frb_server_create(int device, FrbServerRenderFn renderer, void *user);
+void frb_server_destroy(FrbServer *server);
+/* The state changed (GUI: `config != previous_state`): render it, or, if a render is in flight, remember that the
+ * newest state must be rendered once the current frame has been taken.  Never blocks. */
+int frb_server_request(FrbServer *server, const FrbConfig *cfg);
+/* Takes the finished frame if there is one: returns 1 and copies width*height*4 bytes, 0 if none, < 0 if the last render
+ * failed (or `len` is too small).  rgba == NULL peeks: reports the size and leaves the frame in the slot.
+ * timeout_ms: 0 = do not wait, < 0 = wait for a frame. */
+int frb_server_poll(FrbServer *server, uint8_t *rgba, size_t len, uint32_t *width, uint32_t *height, int timeout_ms);
+int frb_server_stats(FrbServer *server, FrbServerStats *stats);
+const char *frb_server_last_error(FrbServer *server);
+
 /* ---- diagnostics ---------------------------------------------------------------------------------------- */
 
 /* Message for the last error on this thread ("" if none). Valid until the next failing call on this thread. */

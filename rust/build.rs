@@ -12,6 +12,7 @@ fn main() {
         .arg(&lib)
         .arg(src.join("frb_api.cu"))
         .arg(src.join("frb_peak.cu"))
+        .arg(src.join("frb_server.cu"))
         .status()
         .expect("nvcc not found");
     assert!(status.success(), "nvcc failed");
