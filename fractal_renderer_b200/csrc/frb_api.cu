@@ -70,7 +70,7 @@ struct DeviceCtx {
     int dev = -1;
     bool ready = false;
     int sm_count = 0;
-    int iter_blocks_per_sm[3] = {0, 0, 0};  // dense FORM 6, dense FORM 7, sparse FORM 6
+    int iter_blocks_per_sm[3] = {0, 0, 0};  // dense FORM 6, dense FORM 7, sparse FORM 6 (deferred: its MINB template argument)
     cudaStream_t stream = nullptr;       // the library's own stream for this device
     cudaStream_t aux[2] = {nullptr, nullptr};  // slab streams of the host-output path
     cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr}, ev_slab[16] = {};
@@ -341,9 +341,27 @@ bool sparse_is_safe(const FrbConfig &cfg)
     return cmax * 1.0000001 <= 0.5 * R * R - 3.0 * R;
 }
 
+// Shape of the deferred kernel (FRB_KERNEL_DEFER6): B iterations per block, NB blocks per trip, MINB resident CTAs per SM.
+// Lanes that stop idle until the trip ends and a stopped pixel costs ~B/2 wasted + ~B/2 resolved iterations, so short
+// pixels want short blocks and trips; the iteration cap is the only a-priori hint.  Measured, profiles/r1_tuning_sweeps.txt.
+void choose_deferred_shape(const FrbConfig &cfg, int *b, int *nb, int *minb)
+{
+    *b = cfg.iterations >= 2048u ? 16 : 8;
+    *nb = cfg.iterations >= 2048u ? 4 : (cfg.iterations >= 256u ? 4 : 1);
+    *minb = 4;
+    if (const char *e = getenv("FRB_TUNE_DB")) *b = atoi(e);      // tuning hooks (bench sweeps)
+    if (const char *e = getenv("FRB_TUNE_NB")) *nb = atoi(e);
+    if (const char *e = getenv("FRB_TUNE_MINB")) *minb = atoi(e);
+    if (*b != 8 && *b != 16 && *b != 32) *b = 16;
+    if (*nb != 1 && *nb != 2 && *nb != 4 && *nb != 8) *nb = 4;
+    if (*b == 32 && *nb == 8) *nb = 4;
+    if (*minb != 4 && *minb != 5) *minb = 4;
+}
+
 struct Plan {
     RenderParams p;
     uint32_t variant;
+    int defer_b, defer_nb, defer_minb;  // deferred kernel: iterations per block, blocks per trip, resident CTAs per SM
     uint64_t npix;
     size_t out_bytes;
 };
@@ -402,9 +420,12 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     uint32_t v = tl_variant;
     // A forced variant is a request: outside its proven domain it is downgraded to the next kernel that is exact
     // (STREAM6 -> DENSE6 -> STREAM7); FrbStats.kernel_variant reports what actually ran.
-    if (v == FRB_KERNEL_AUTO || v == FRB_KERNEL_STREAM6) v = sparse_is_safe(cfg) ? FRB_KERNEL_STREAM6 : FRB_KERNEL_DENSE6;
+    if (v == FRB_KERNEL_AUTO || v == FRB_KERNEL_DEFER6) v = sparse_is_safe(cfg) ? FRB_KERNEL_DEFER6 : FRB_KERNEL_DENSE6;
+    if (v == FRB_KERNEL_STREAM6) v = sparse_is_safe(cfg) ? FRB_KERNEL_STREAM6 : FRB_KERNEL_DENSE6;
     if (v == FRB_KERNEL_DENSE6 && !form6_is_exact(cfg)) v = FRB_KERNEL_STREAM7;
     plan->variant = v;
+    choose_deferred_shape(cfg, &plan->defer_b, &plan->defer_nb, &plan->defer_minb);
+    p.defer_block = (uint32_t)plan->defer_b;
 
     if (int rc = ensure(c.b().tab, c.b().tab_cap, (size_t)cfg.width + cfg.height + 2)) return rc;
     if (int rc = ensure(c.b().iters, c.b().iters_cap, (size_t)npix + 4)) return rc;
@@ -427,8 +448,39 @@ int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaSt
         frb::frb_iterate_simple_kernel<<<grid, 256, 0, st>>>(p);
         return FRB_OK;
     }
-    const int kidx = (plan.variant == FRB_KERNEL_STREAM7) ? 1 : (plan.variant == FRB_KERNEL_DENSE6 ? 0 : 2);
     const uint32_t warps_per_block = frb::kIterateThreads / 32;
+    if (plan.variant == FRB_KERNEL_DEFER6) {
+        uint32_t blocks = (uint32_t)(c.sm_count * plan.defer_minb);
+        const uint32_t needed = (p.total_chunks + warps_per_block - 1) / warps_per_block;
+        blocks = std::max(1u, std::min(blocks, needed));
+        const bool julia = (p.algo == FRB_ALGO_JULIA);
+        const int key = plan.defer_b * 100 + plan.defer_nb * 10 + plan.defer_minb;
+#define FRB_DEFER_CASE(B, NB, M)                                                                              \
+    case (B) * 100 + (NB) * 10 + (M):                                                                        \
+        if (julia) frb::frb_iterate_deferred_kernel<true, B, NB, M><<<blocks, frb::kIterateThreads, 0, st>>>(p);  \
+        else frb::frb_iterate_deferred_kernel<false, B, NB, M><<<blocks, frb::kIterateThreads, 0, st>>>(p);       \
+        break;
+#define FRB_DEFER_CASES(B, NB) FRB_DEFER_CASE(B, NB, 4) FRB_DEFER_CASE(B, NB, 5)
+        switch (key) {
+            FRB_DEFER_CASES(8, 1) FRB_DEFER_CASES(8, 2) FRB_DEFER_CASES(8, 4) FRB_DEFER_CASES(8, 8)
+            FRB_DEFER_CASES(16, 1) FRB_DEFER_CASES(16, 2) FRB_DEFER_CASES(16, 4) FRB_DEFER_CASES(16, 8)
+            FRB_DEFER_CASES(32, 1) FRB_DEFER_CASES(32, 2) FRB_DEFER_CASES(32, 4)
+        default:
+            return fail(FRB_ERR_INVALID, "no deferred kernel for block %d x %d, %d CTAs/SM", plan.defer_b, plan.defer_nb, plan.defer_minb);
+        }
+#undef FRB_DEFER_CASES
+#undef FRB_DEFER_CASE
+        // K1r over the rows this launch covered (a row slab of the shard, or all of it)
+        RenderParams r = p;
+        r.resolve_row0 = p.chunks_per_row ? p.chunk_begin / p.chunks_per_row : 0u;
+        r.resolve_rows = p.chunks_per_row ? p.total_chunks / p.chunks_per_row : 0u;
+        if (r.resolve_rows > 0) {
+            dim3 grid(r.resolve_rows, (p.width + 255) / 256);
+            frb::frb_resolve_kernel<<<grid, 256, 0, st>>>(r);
+        }
+        return FRB_OK;
+    }
+    const int kidx = (plan.variant == FRB_KERNEL_STREAM7) ? 1 : (plan.variant == FRB_KERNEL_DENSE6 ? 0 : 2);
     uint32_t blocks = (uint32_t)(c.sm_count * c.iter_blocks_per_sm[kidx]);
     const uint32_t needed = (p.total_chunks + warps_per_block - 1) / warps_per_block;
     blocks = std::max(1u, std::min(blocks, needed));
@@ -503,7 +555,7 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
         slot.launches++;
         if (p.algo != FRB_ALGO_BARNSLEY_FERN) {
             if (int rc = launch_iterate(c, plan, p, st)) return rc;
-            slot.launches++;
+            slot.launches += (plan.variant == FRB_KERNEL_DEFER6) ? 2 : 1;  // DEFER6 = iterate + resolve
         } else {
             // get_recursive_pixel returns BLACK without iterating (calc/src/lib.rs:211); keep the raw outputs defined
             CU(cudaMemsetAsync(p.iters, 0, plan.npix * sizeof(uint32_t), st));
@@ -562,7 +614,7 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
         sh.zfinal = p.zfinal + pix0;
         sh.out = p.out + pix0 * p.format;
         launch_shade(c, sh, ks);
-        slot.launches += 2;
+        slot.launches += (plan.variant == FRB_KERNEL_DEFER6) ? 3 : 2;
         if (pipeline) {
             CU(cudaEventRecord(c.ev_slab[s % 16], ks));
             CU(cudaStreamWaitEvent(cs, c.ev_slab[s % 16], 0));
@@ -767,7 +819,7 @@ void frb_shutdown(void)
 
 int frb_set_kernel_variant(uint32_t variant)
 {
-    if (variant > FRB_KERNEL_DENSE6) return fail(FRB_ERR_INVALID, "unknown kernel variant %u", variant);
+    if (variant > FRB_KERNEL_DEFER6) return fail(FRB_ERR_INVALID, "unknown kernel variant %u", variant);
     tl_variant = variant;
     return FRB_OK;
 }

@@ -53,7 +53,9 @@ struct RenderParams {
     uint32_t format;       // 3 = RGB24, 4 = RGBA32
     uint32_t filter_abs_hi; // high word of sqrt(S/2), minus 1: max(|re|,|im|) >= this is necessary for re^2+im^2 > S/2
     uint32_t chunk_begin;   // first chunk of this launch (row slabs of one shard are separate launches); 0 normally
-    uint32_t pad1;
+    uint32_t defer_block;   // K1c/K1r: iterations per block of the deferred kernel (a record is at most this + 1 steps short)
+    uint32_t resolve_row0;  // K1r: first local row and number of rows to resolve
+    uint32_t resolve_rows;
     // buffers
     double *tab_re;              // [width]   re0(x)
     double *tab_im;              // [height]  im0(y), indexed by IMAGE row
@@ -316,7 +318,8 @@ frb_iterate_stream_kernel(const __grid_constant__ RenderParams p)
 
 }  // namespace frb
 
-#include "frb_sparse.cuh"  // K1b: the default iterate kernel (sparse escape checks, inline-PTX trip)
+#include "frb_sparse.cuh"    // K1b: sparse escape checks, positions of the last block recorded in registers
+#include "frb_deferred.cuh"  // K1c + K1r: the default — no recorded positions, escapes resolved by a second pass
 
 namespace frb {
 

@@ -123,7 +123,7 @@ typedef struct FrbStats {
 } FrbStats;
 
 enum {
-    FRB_KERNEL_AUTO = 0,      /* STREAM6 when its preconditions hold (every sane input), else DENSE6, else STREAM7 */
+    FRB_KERNEL_AUTO = 0,      /* DEFER6 when its preconditions hold (every sane input), else DENSE6, else STREAM7 */
     FRB_KERNEL_STREAM6 = 1,   /* persistent lane-refill kernel, 6 FP64 instructions / iteration, one escape filter per
                                  block of 8 iterations (needs limit >= 8 and |c| <= limit^2/2 - 3 limit: an escaped orbit
                                  then provably keeps growing) */
@@ -131,7 +131,10 @@ enum {
                                  iteration: exact for ANY input */
     FRB_KERNEL_SIMPLE = 3,    /* one thread per pixel, reference operation order as written (11 FP64 instructions), no
                                  queue: the on-GPU cross-check for the others */
-    FRB_KERNEL_DENSE6 = 4     /* as STREAM6 but with the filter every iteration (small limits, short iteration caps) */
+    FRB_KERNEL_DENSE6 = 4,    /* as STREAM6 but with the filter every iteration (small limits, short iteration caps) */
+    FRB_KERNEL_DEFER6 = 5     /* the default where STREAM6's preconditions hold: same arithmetic, nothing recorded in the
+                                 loop; a stopped lane stores the position at the start of its last block and a resolve
+                                 pass re-runs <= block+1 iterations with the reference's test after every step */
 };
 
 /* ---- lifecycle ------------------------------------------------------------------------------------------ */

@@ -59,18 +59,19 @@ def test_small_cases_vs_oracle_and_golden(gpu, name):
     assert_parity(gpu, cfg, golden, what=name + "/auto")
 
 
-@pytest.mark.parametrize("variant", ["stream6", "dense6", "stream7", "simple"])
+@pytest.mark.parametrize("variant", ["defer6", "stream6", "dense6", "stream7", "simple"])
 @pytest.mark.parametrize("name", ["mandel_default", "mandel_iter0", "mandel_iter9", "mandel_limit1p5", "mandel_limit1e155",
                                   "mandel_limit_nan", "mandel_real_axis", "mandel_deep_subulp", "julia_default",
                                   "julia_c3_view", "C1_small", "C2_small", "C4_small"])
 def test_every_kernel_variant(gpu, name, variant):
     """Forcing each kernel: STREAM7 and SIMPLE are exact for any input; STREAM6 is exact for these (sane) inputs."""
     cfg = SMALL[name]
-    v = {"stream6": gpu.KERNEL_STREAM6, "dense6": gpu.KERNEL_DENSE6, "stream7": gpu.KERNEL_STREAM7, "simple": gpu.KERNEL_SIMPLE}[variant]
+    v = {"defer6": gpu.KERNEL_DEFER6, "stream6": gpu.KERNEL_STREAM6, "dense6": gpu.KERNEL_DENSE6, "stream7": gpu.KERNEL_STREAM7, "simple": gpu.KERNEL_SIMPLE}[variant]
     ref = ob.render_rows(cfg, threads=1)
     _, stats = assert_parity(gpu, cfg, ref, variant=v, what=f"{name}/{variant}")
     # a forced kernel is downgraded (STREAM6 -> DENSE6 -> STREAM7) outside its proven domain, never run unsafely
-    chain = {gpu.KERNEL_STREAM6: (gpu.KERNEL_STREAM6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7),
+    chain = {gpu.KERNEL_DEFER6: (gpu.KERNEL_DEFER6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7),
+             gpu.KERNEL_STREAM6: (gpu.KERNEL_STREAM6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7),
              gpu.KERNEL_DENSE6: (gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7)}.get(v, (v,))
     assert stats["kernel_variant"] in chain
     if name in ("mandel_default", "C2_small", "C4_small", "julia_default"):
@@ -78,13 +79,13 @@ def test_every_kernel_variant(gpu, name, variant):
 
 
 def test_auto_routes_exotic_inputs_to_form7(gpu):
-    for name, expect in [("mandel_default", gpu.KERNEL_STREAM6), ("julia_default", gpu.KERNEL_STREAM6),
+    for name, expect in [("mandel_default", gpu.KERNEL_DEFER6), ("julia_default", gpu.KERNEL_DEFER6),
                          ("julia_zero", gpu.KERNEL_STREAM7), ("julia_real_c", gpu.KERNEL_STREAM7),
                          ("julia_tiny_im", gpu.KERNEL_STREAM7), ("mandel_limit1e155", gpu.KERNEL_STREAM7),
                          ("mandel_limit_nan", gpu.KERNEL_STREAM7), ("mandel_huge_coords", gpu.KERNEL_STREAM7),
-                         ("mandel_real_axis", gpu.KERNEL_STREAM6), ("mandel_limit2", gpu.KERNEL_DENSE6),
+                         ("mandel_real_axis", gpu.KERNEL_DEFER6), ("mandel_limit2", gpu.KERNEL_DENSE6),
                          ("mandel_limit1p5", gpu.KERNEL_DENSE6), ("mandel_iter7", gpu.KERNEL_DENSE6),
-                         ("mandel_far_out", gpu.KERNEL_STREAM6), ("C4_small", gpu.KERNEL_STREAM6)]:
+                         ("mandel_far_out", gpu.KERNEL_DEFER6), ("C4_small", gpu.KERNEL_DEFER6)]:
         gpu.render_counts(SMALL[name])
         assert gpu.last_stats()["kernel_variant"] == expect, name
 
@@ -147,7 +148,7 @@ def test_full_size_properties_c2_variants_agree(gpu):
     written, on the GPU) and hit the exact iteration total."""
     cfg = configs.c2()
     res = {}
-    for v in (gpu.KERNEL_STREAM6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7, gpu.KERNEL_SIMPLE):
+    for v in (gpu.KERNEL_DEFER6, gpu.KERNEL_STREAM6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7, gpu.KERNEL_SIMPLE):
         gpu.set_kernel_variant(v)
         try:
             res[v] = gpu.render_counts(cfg)
@@ -155,7 +156,7 @@ def test_full_size_properties_c2_variants_agree(gpu):
         finally:
             gpu.set_kernel_variant(gpu.KERNEL_AUTO)
     base = res[gpu.KERNEL_SIMPLE]
-    for v in (gpu.KERNEL_STREAM6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7):
+    for v in (gpu.KERNEL_DEFER6, gpu.KERNEL_STREAM6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7):
         assert np.array_equal(res[v][0], base[0])
         assert z_equal(res[v][1], base[1]).all()
 
