@@ -426,6 +426,8 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     plan->variant = v;
     choose_deferred_shape(cfg, &plan->defer_b, &plan->defer_nb, &plan->defer_minb);
     p.defer_block = (uint32_t)plan->defer_b;
+    // DEFER6 leaves provisional records; the shade kernel resolves them on the fly, the raw-result path (format 0) runs K1r
+    p.records = (v == FRB_KERNEL_DEFER6 && format != 0) ? 1u : 0u;
 
     if (int rc = ensure(c.b().tab, c.b().tab_cap, (size_t)cfg.width + cfg.height + 2)) return rc;
     if (int rc = ensure(c.b().iters, c.b().iters_cap, (size_t)npix + 4)) return rc;
@@ -470,11 +472,11 @@ int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaSt
         }
 #undef FRB_DEFER_CASES
 #undef FRB_DEFER_CASE
-        // K1r over the rows this launch covered (a row slab of the shard, or all of it)
+        // raw-result path: K1r over the rows this launch covered (with an image format the shade kernel resolves instead)
         RenderParams r = p;
         r.resolve_row0 = p.chunks_per_row ? p.chunk_begin / p.chunks_per_row : 0u;
         r.resolve_rows = p.chunks_per_row ? p.total_chunks / p.chunks_per_row : 0u;
-        if (r.resolve_rows > 0) {
+        if (p.records == 0u && r.resolve_rows > 0) {
             dim3 grid(r.resolve_rows, (p.width + 255) / 256);
             frb::frb_resolve_kernel<<<grid, 256, 0, st>>>(r);
         }
@@ -555,7 +557,7 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
         slot.launches++;
         if (p.algo != FRB_ALGO_BARNSLEY_FERN) {
             if (int rc = launch_iterate(c, plan, p, st)) return rc;
-            slot.launches += (plan.variant == FRB_KERNEL_DEFER6) ? 2 : 1;  // DEFER6 = iterate + resolve
+            slot.launches += (plan.variant == FRB_KERNEL_DEFER6 && p.records == 0u) ? 2 : 1;  // raw DEFER6 = iterate + resolve
         } else {
             // get_recursive_pixel returns BLACK without iterating (calc/src/lib.rs:211); keep the raw outputs defined
             CU(cudaMemsetAsync(p.iters, 0, plan.npix * sizeof(uint32_t), st));
@@ -610,11 +612,12 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
         RenderParams sh = p;  // shade: the slab's pixels through offset pointers
         const size_t pix0 = (size_t)r0 * p.width;
         sh.rows = r1 - r0;
+        sh.resolve_row0 = r0;
         sh.iters = p.iters + pix0;
         sh.zfinal = p.zfinal + pix0;
         sh.out = p.out + pix0 * p.format;
         launch_shade(c, sh, ks);
-        slot.launches += (plan.variant == FRB_KERNEL_DEFER6) ? 3 : 2;
+        slot.launches += 2;
         if (pipeline) {
             CU(cudaEventRecord(c.ev_slab[s % 16], ks));
             CU(cudaStreamWaitEvent(cs, c.ev_slab[s % 16], 0));

@@ -210,6 +210,7 @@ __device__ __forceinline__ void resolve_record(const RenderParams &p, uint32_t &
     const double S = p.limit_sq;
     const uint32_t filter_hi = p.filter_hi;
     count = iterations;
+    // (Splitting this into a filter-only inner loop with the FP64 compare outside it was measured slower: C2 0.205 vs 0.177 ms.)
     for (uint32_t k = 0; k < steps; ++k) {
         stream_core<6>(o);
         if (stream_filter(o, filter_hi) && stream_escaped(o, S)) {

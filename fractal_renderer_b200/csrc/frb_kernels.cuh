@@ -56,6 +56,9 @@ struct RenderParams {
     uint32_t defer_block;   // K1c/K1r: iterations per block of the deferred kernel (a record is at most this + 1 steps short)
     uint32_t resolve_row0;  // K1r: first local row and number of rows to resolve
     uint32_t resolve_rows;
+    uint32_t records;       // K2: 1 = iters/zfinal hold K1c's provisional records; resolve them while shading (local row 0 of the
+                            // pointers is shard row resolve_row0)
+    uint32_t pad2;
     // buffers
     double *tab_re;              // [width]   re0(x)
     double *tab_im;              // [height]  im0(y), indexed by IMAGE row
@@ -407,20 +410,56 @@ frb_shade_kernel(const __grid_constant__ RenderParams p)
     for (uint64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const uint64_t base = blk * cta_px + (uint64_t)threadIdx.x * kShadePxPerThread;
         uint32_t c[4] = {0u, 0u, 0u, 0u};
+        // position of the thread's first pixel (only needed to look up c when provisional records are resolved here)
+        uint32_t lr = 0, px = 0;
+        double c_im = 0.0;
+        const bool lookup = p.records != 0u && p.algo != kAlgoJulia && base < npix;
+        if (lookup) {
+            const uint32_t row = (uint32_t)(base / p.width);
+            px = (uint32_t)(base - (uint64_t)row * p.width);
+            lr = p.resolve_row0 + row;
+            c_im = __ldg(p.tab_im + local_row_to_y(p, lr));
+        }
         if (base + 4 <= npix) {
             const uint4 n4 = *reinterpret_cast<const uint4 *>(p.iters + base);
-            const uint32_t n[4] = {n4.x, n4.y, n4.z, n4.w};
+            uint32_t n[4] = {n4.x, n4.y, n4.z, n4.w};
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                c[k] = shade_pixel(p, n[k], p.zfinal[base + k]);
+                double2 z = p.zfinal[base + k];
+                if (p.records != 0u) {
+                    double cr = p.julia_re, ci = p.julia_im;
+                    if (lookup) {
+                        cr = __ldg(p.tab_re + px);
+                        ci = c_im;
+                        if (++px == p.width && k < 3) {
+                            px = 0;
+                            c_im = __ldg(p.tab_im + local_row_to_y(p, ++lr));
+                        }
+                    }
+                    resolve_record(p, n[k], z, cr, ci);
+                }
+                c[k] = shade_pixel(p, n[k], z);
                 useful += min(n[k], p.iterations - 1u) + 1u;
             }
         } else {
 #pragma unroll
             for (int k = 0; k < 4; ++k)
                 if (base + k < npix) {
-                    const uint32_t n = p.iters[base + k];
-                    c[k] = shade_pixel(p, n, p.zfinal[base + k]);
+                    uint32_t n = p.iters[base + k];
+                    double2 z = p.zfinal[base + k];
+                    if (p.records != 0u) {
+                        double cr = p.julia_re, ci = p.julia_im;
+                        if (lookup) {
+                            cr = __ldg(p.tab_re + px);
+                            ci = c_im;
+                            if (++px == p.width && base + k + 1 < npix) {
+                                px = 0;
+                                c_im = __ldg(p.tab_im + local_row_to_y(p, ++lr));
+                            }
+                        }
+                        resolve_record(p, n, z, cr, ci);
+                    }
+                    c[k] = shade_pixel(p, n, z);
                     useful += min(n, p.iterations - 1u) + 1u;
                 }
         }
