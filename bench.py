@@ -338,7 +338,7 @@ def main():
     achieved_tflops = per_launch_iters * FLOP_PER_ITER / (it_ms * 1e-3) / 1e12
     peak_tflops = peak["dfma_per_s"] * 2 / 1e12
     form = {frb.KERNEL_DEFER6: 6, frb.KERNEL_STREAM6: 6, frb.KERNEL_DENSE6: 6, frb.KERNEL_STREAM7: 7}.get(kernel_variant, 11)
-    kname = {frb.KERNEL_DEFER6: "frb_iterate_deferred_kernel<6> + frb_resolve_kernel", frb.KERNEL_STREAM6: "frb_iterate_sparse_kernel<6>", frb.KERNEL_DENSE6: "frb_iterate_stream_kernel<6>",
+    kname = {frb.KERNEL_DEFER6: "frb_iterate_deferred_kernel<6>", frb.KERNEL_STREAM6: "frb_iterate_sparse_kernel<6>", frb.KERNEL_DENSE6: "frb_iterate_stream_kernel<6>",
              frb.KERNEL_STREAM7: "frb_iterate_stream_kernel<7>"}.get(kernel_variant, "frb_iterate_simple_kernel")
     traffic = None
     try:
@@ -354,6 +354,7 @@ def main():
         "traffic_note": "DRAM bytes read+written by this kernel per launch from one ncu --set full capture (profiles/r1_traffic.json); algorithmic = 20 B/px raw result written, 0 read",
         "kernel": kname,
         "kernel_ms": round(it_ms, 4), "shade_kernel_ms": round(statistics.mean(shade_ms), 4),
+        "shade_kernel_note": "frb_shade_kernel; with the defer6 iterate kernel it also resolves each pixel's provisional record (<= block+1 iterations with the reference's test)",
         "kernel_share_of_step": round(it_ms * args.steps / dev_ms, 4) if world == 1 else None,
         "peak_source": "measured in this run: frb_measure_fp64_peak DFMA stream x 2 flop (MEASURED_PEAKS.json has no FP64 entry)",
         "peak_nominal": FP64_NOMINAL_TFLOPS, "frac_of_nominal": round(achieved_tflops / FP64_NOMINAL_TFLOPS, 4),

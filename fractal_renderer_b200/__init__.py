@@ -8,6 +8,7 @@ Host-side mirror of the reference's public interface for this path (same names a
     get_image(&Config) -> Vec<RGB>  (src/lib.rs:253)   get_image(config) -> (H*W, 3) uint8 array
     GUI's RGBA expansion            (src/gui.rs:62-75) get_image_rgba(config) -> (H, W, 4) uint8 array
     calc::recursive per pixel       (calc/src/lib.rs:245) render_counts(config) -> (iters, zfinal)
+    get_image's BarnsleyFern arm    (src/lib.rs:271-319) render_fern(config, threads, seed)
 
 All pixels are computed by the CUDA library behind include/frb.h (libfrb.so); nothing here computes a pixel on the
 CPU, and nothing here imports oracle/.
@@ -15,6 +16,7 @@ CPU, and nothing here imports oracle/.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional, Sequence
 
 import numpy as np
@@ -27,7 +29,7 @@ from .calc import RGB, Algo, Config, FrbConfig, Imaginary
 __all__ = [
     "Algo", "Config", "Imaginary", "RGB", "FrbError", "Shard", "get_image", "get_image_rgba", "get_image_into",
     "render_shard", "render_counts", "render_frames", "render_device_async", "sync_stats", "async_stats", "last_stats",
-    "device_count", "init", "shutdown", "set_kernel_variant", "measure_fp64_peak", "shard_rows", "shard_row_to_y",
+    "device_count", "init", "shutdown", "render_fern", "fern_default_threads", "set_kernel_variant", "measure_fp64_peak", "shard_rows", "shard_row_to_y",
     "FRB_RGB24", "FRB_RGBA32", "KERNEL_AUTO", "KERNEL_STREAM6", "KERNEL_STREAM7", "KERNEL_SIMPLE", "KERNEL_DENSE6", "KERNEL_DEFER6", "KERNEL_NAMES",
 ]
 
@@ -103,9 +105,33 @@ def get_image_into(config: Config, out: np.ndarray, fmt: int = FRB_RGB24, device
 
 
 def get_image(config: Config, device: int = 0) -> np.ndarray:
-    """`get_image(&Config) -> Vec<RGB>` (src/lib.rs:253): (H*W, 3) uint8, row-major, fields r,g,b."""
+    """`get_image(&Config) -> Vec<RGB>` (src/lib.rs:253): (H*W, 3) uint8, row-major, fields r,g,b.  Like the reference it
+    dispatches on the algorithm: Mandelbrot | Julia -> the per-pixel path, BarnsleyFern -> the chaos game with rayon's
+    thread count and a fresh entropy seed (src/lib.rs:271-319, 428)."""
+    if config.algo == Algo.BarnsleyFern:
+        return render_fern(config, device=max(device, 0)).reshape(-1, 3)
     out = np.empty((config.height * config.width, 3), np.uint8)
     return get_image_into(config, out, FRB_RGB24, device)
+
+
+def fern_default_threads() -> int:
+    """rayon::current_num_threads() as the reference would see it on this host (RAYON_NUM_THREADS or the logical CPUs)."""
+    return int(_lib.load().frb_fern_default_threads())
+
+
+def render_fern(config: Config, threads: int = 0, seed: Optional[int] = None, shard: Optional[Shard] = None,
+                fmt: int = FRB_RGB24, device: int = 0) -> np.ndarray:
+    """get_image's BarnsleyFern arm (src/lib.rs:271-319): (rows, W, fmt) uint8.  `threads` = the reference's rayon thread
+    count T (0 = this host's), `seed` replaces SmallRng::from_entropy (None = fresh entropy, as the reference)."""
+    if seed is None:
+        seed = int.from_bytes(os.urandom(8), "little")
+    rows = shard_rows(config.height, shard)
+    out = np.empty((rows, config.width, fmt), np.uint8)
+    c = config.to_c()
+    s, p = _shard_ptr(shard)
+    _lib.check(_lib.load().frb_render_fern(ctypes.byref(c), threads, seed & 0xFFFFFFFFFFFFFFFF, p, out.ctypes.data, out.nbytes,
+                                           fmt, device))
+    return out
 
 
 def get_image_rgba(config: Config, device: int = 0) -> np.ndarray:

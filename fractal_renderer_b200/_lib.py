@@ -45,6 +45,8 @@ EXPORTS = (
     "frb_render_shard",
     "frb_render_counts",
     "frb_render_frames",
+    "frb_render_fern",
+    "frb_fern_default_threads",
     "frb_render_device_async",
     "frb_sync_stats",
     "frb_async_stats",
@@ -126,6 +128,11 @@ def load() -> ctypes.CDLL:
     P = ctypes.POINTER
     L.frb_abi_version.restype = ctypes.c_uint32
     L.frb_abi_version.argtypes = []
+    L.frb_render_fern.restype = ctypes.c_int
+    L.frb_render_fern.argtypes = [P(FrbConfig), ctypes.c_uint32, ctypes.c_uint64, P(FrbShard), ctypes.c_void_p, ctypes.c_size_t,
+                                  ctypes.c_uint32, ctypes.c_int]
+    L.frb_fern_default_threads.restype = ctypes.c_uint32
+    L.frb_fern_default_threads.argtypes = []
     L.frb_config_default.restype = None
     L.frb_config_default.argtypes = [P(FrbConfig), ctypes.c_uint32]
     L.frb_shard_rows.restype = ctypes.c_uint32

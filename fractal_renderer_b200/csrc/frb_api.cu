@@ -18,6 +18,9 @@
 #include <vector>
 
 #include "frb_kernels.cuh"
+#include "frb_fern.cuh"
+
+#include <thread>
 
 namespace {
 
@@ -93,6 +96,13 @@ struct DeviceCtx {
     } sets[2];
     int cur_set = 0;
     BufSet &b() { return sets[cur_set]; }
+    // Barnsley fern (frb_render_fern): per-virtual-thread hit counts and the colour table, grow-only
+    uint32_t *fern_counts = nullptr;
+    size_t fern_counts_cap = 0;
+    uint32_t *fern_lut = nullptr;
+    uint8_t *fern_out = nullptr;
+    size_t fern_out_cap = 0;
+    cudaEvent_t ev_fern[2] = {nullptr, nullptr};
     std::mutex mu;
     Slot slots[kSlots];
     uint32_t next_slot = 0;
@@ -179,6 +189,11 @@ void ctx_destroy(DeviceCtx *c)
             if (s.ev_end) cudaEventDestroy(s.ev_end);
             if (s.host) cudaFreeHost(s.host);
         }
+        cudaFree(c->fern_counts);
+        cudaFree(c->fern_lut);
+        cudaFree(c->fern_out);
+        for (auto &e : c->ev_fern)
+            if (e) cudaEventDestroy(e);
         if (c->ev_fork) cudaEventDestroy(c->ev_fork);
         for (auto &e : c->ev_slab)
             if (e) cudaEventDestroy(e);
@@ -833,6 +848,117 @@ int frb_render_shard(const FrbConfig *cfg, const FrbShard *shard, uint8_t *out, 
     if (format != FRB_RGB24 && format != FRB_RGBA32) return fail(FRB_ERR_INVALID, "unknown pixel format %u", format);
     const FrbShard s = shard ? *shard : whole_frame();
     return render_blocking(*cfg, s, device, format, out, out_len, nullptr, nullptr);
+}
+
+uint32_t frb_fern_default_threads(void)
+{
+    // rayon::current_num_threads() of the global pool: RAYON_NUM_THREADS if set to a positive number, else the logical CPUs
+    if (const char *e = getenv("RAYON_NUM_THREADS")) {
+        const long v = atol(e);
+        if (v > 0) return (uint32_t)std::min<long>(v, 65536);
+    }
+    const unsigned hc = std::thread::hardware_concurrency();
+    return hc ? hc : 1u;
+}
+
+int frb_render_fern(const FrbConfig *cfg, uint32_t threads, uint64_t seed, const FrbShard *shard, uint8_t *out, size_t out_len,
+                    uint32_t format, int device)
+{
+    const double t0 = now_ms();
+    if (!cfg) return fail(FRB_ERR_INVALID, "null config");
+    if (format != FRB_RGB24 && format != FRB_RGBA32) return fail(FRB_ERR_INVALID, "unknown pixel format %u", format);
+    const FrbShard sh = shard ? *shard : whole_frame();
+    if (!shard_valid(sh)) return fail(FRB_ERR_INVALID, "bad shard: index %u of count %u", sh.index, sh.count);
+    if (threads == 0) threads = frb_fern_default_threads();
+    if (threads > 65536u) return fail(FRB_ERR_INVALID, "fern: %u virtual threads (max 65536)", threads);
+    DeviceCtx *c = get_ctx(device < 0 ? 0 : device);
+    if (!c) return tl_code;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->dev));
+
+    frb::FernParams p;
+    memset(&p, 0, sizeof p);
+    p.width = cfg->width;
+    p.height = cfg->height;
+    p.threads = threads;
+    p.per = cfg->iterations / threads;  // `config.iterations / threads` (src/lib.rs:286): the remainder is dropped
+    {
+        const uint64_t chains = std::min<uint64_t>(std::max<uint64_t>(((uint64_t)p.per + 511u) / 512u, 1u), 65536u);
+        p.chains = (uint32_t)chains;
+    }
+    p.format = format;
+    p.rows = shard_rows(cfg->height, sh);
+    p.band_rows = shard_band_rows(cfg->height, sh);
+    p.shard_index = sh.index;
+    p.shard_count = sh.count;
+    p.primary = (uint32_t)cfg->primary_color.r | ((uint32_t)cfg->primary_color.g << 8) | ((uint32_t)cfg->primary_color.b << 16);
+    p.secondary = (uint32_t)cfg->secondary_color.r | ((uint32_t)cfg->secondary_color.g << 8) | ((uint32_t)cfg->secondary_color.b << 16);
+    p.seed = seed;
+    p.npix = (uint64_t)cfg->width * cfg->height;
+    p.pos_re = cfg->pos.re;
+    p.pos_im = cfg->pos.im;
+    p.wf = (double)cfg->width;
+    p.hf = (double)cfg->height;
+    {
+        // `65.0 * config.scale.re * config.height as f64 * 0.006` (src/lib.rs:425-426), left to right, one rounding each
+        volatile double a = 65.0 * cfg->scale.re;
+        volatile double b = a * (double)cfg->height;
+        volatile double cx = b * 0.006;
+        p.esx = cx;
+        volatile double d = 37.0 * cfg->scale.im;
+        volatile double e = d * (double)cfg->height;
+        volatile double cy = e * 0.006;
+        p.esy = cy;
+    }
+    p.amount = cfg->color_weight;
+
+    const size_t out_bytes = (size_t)p.rows * cfg->width * format;
+    if (out_len < out_bytes) return fail(FRB_ERR_INVALID, "output buffer too small: %zu < %zu bytes", out_len, out_bytes);
+    if (out_bytes && !out) return fail(FRB_ERR_INVALID, "null output buffer");
+    if (p.npix * threads > (1ull << 34))
+        return fail(FRB_ERR_TOO_LARGE, "fern: %u images of %llu pixels exceed the hit-count budget (2^34 counters)", threads,
+                    (unsigned long long)p.npix);
+    FrbStats s = {};
+    s.pixels = (uint64_t)p.rows * cfg->width;
+    s.iterations = (uint64_t)p.per * threads;  // plotted points
+    s.devices = 1;
+    if (p.npix == 0 || out_bytes == 0) {
+        tl_stats = s;
+        return FRB_OK;
+    }
+    if (int rc = ensure(c->fern_counts, c->fern_counts_cap, (size_t)(p.npix * threads))) return rc;
+    if (int rc = ensure(c->fern_out, c->fern_out_cap, out_bytes + 64)) return rc;
+    if (!c->fern_lut) CU(cudaMalloc(&c->fern_lut, frb::kFernLut * sizeof(uint32_t)));
+    for (auto &e : c->ev_fern)
+        if (!e) CU(cudaEventCreate(&e));
+    p.counts = c->fern_counts;
+    p.lut = c->fern_lut;
+    p.out = c->fern_out;
+
+    cudaStream_t st = c->stream;
+    CU(cudaEventRecord(c->ev_fern[0], st));
+    CU(cudaMemsetAsync(p.counts, 0, (size_t)(p.npix * threads) * sizeof(uint32_t), st));
+    frb::frb_fern_lut_kernel<<<1, 32, 0, st>>>(p);
+    const uint64_t nchains = (uint64_t)threads * p.chains;
+    if (p.per > 0)
+        frb::frb_fern_chaos_kernel<<<(unsigned)((nchains + frb::kFernThreads - 1) / frb::kFernThreads), frb::kFernThreads, 0, st>>>(p);
+    {
+        const uint64_t n_out = (uint64_t)p.rows * cfg->width;
+        const unsigned grid = (unsigned)std::min<uint64_t>((n_out + 255) / 256, (uint64_t)c->sm_count * 32);
+        frb::frb_fern_compose_kernel<<<grid, 256, 0, st>>>(p);
+    }
+    CU(cudaEventRecord(c->ev_fern[1], st));
+    CU(cudaMemcpyAsync(out, p.out, out_bytes, cudaMemcpyDeviceToHost, st));
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, c->ev_fern[0], c->ev_fern[1]));
+    s.iterate_ms = ms;
+    s.device_ms = ms;
+    s.total_ms = (float)(now_ms() - t0);
+    s.kernel_launches = p.per > 0 ? 3u : 2u;
+    tl_stats = s;
+    return FRB_OK;
 }
 
 int frb_render_counts(const FrbConfig *cfg, const FrbShard *shard, uint32_t *iters, double *zfinal, int device)

@@ -49,7 +49,7 @@ typedef struct FrbRGB {
 /* calc::Algo (calc/src/lib.rs:150-154), declaration order. */
 enum {
     FRB_ALGO_MANDELBROT = 0,
-    FRB_ALGO_BARNSLEY_FERN = 1, /* not on this path: rendered as all-black, as get_recursive_pixel does (:211) */
+    FRB_ALGO_BARNSLEY_FERN = 1, /* frb_render*: all-black, as get_recursive_pixel does (:211); the chaos game is frb_render_fern */
     FRB_ALGO_JULIA = 2
 };
 
@@ -68,7 +68,7 @@ typedef struct FrbConfig {
     uint8_t smooth;
     FrbRGB primary_color;
     FrbRGB secondary_color;
-    double color_weight;  /* fern only; carried for layout fidelity, unused */
+    double color_weight;  /* fern only (frb_render_fern): subtract_pixel's `amount` */
     FrbImaginary julia_set;
 } FrbConfig;
 
@@ -171,6 +171,23 @@ int frb_render_counts(const FrbConfig *cfg, const FrbShard *shard, uint32_t *ite
  * all to `device`; out holds the frames back to back, each width_k*height_k*format bytes. */
 int frb_render_frames(const FrbConfig *cfgs, uint32_t n, uint8_t *out, size_t out_len, uint32_t format,
                       int device);
+
+/* ---- Barnsley fern: the other arm of get_image (src/lib.rs:271-319, 417-463) --------------------------------- */
+
+/* Replaces get_image's BarnsleyFern arm.  The reference plays the chaos game on T = rayon threads, each with an
+ * entropy-seeded generator and its own image (initialised to secondary_color, darkened under every plotted point by
+ * subtract_pixel), for iterations / T points each, and reduces the T images with a saturating add; its output
+ * therefore depends on the host's thread count and differs from run to run.  Here `threads` is that T (0 = what rayon
+ * would use on this host: RAYON_NUM_THREADS or the logical CPUs) and `seed` replaces the entropy: the image is a pure
+ * function of (cfg, threads, seed), reproduced bit for bit by oracle/fern_oracle.c.  Each of the T shares is played as
+ * ceil(share / 512) independent chains (xoshiro256++ streams seeded seed + (chain+1) * 0xD1342543DE82EF95 via
+ * splitmix64; chains after a share's first discard 64 burn-in points).  `shard` (NULL = whole frame) selects the rows
+ * written to `out`, compact as for frb_render_shard; every shard plays the whole game (10^7 points are microseconds).
+ * frb_render* with algo = FRB_ALGO_BARNSLEY_FERN keep the per-pixel semantics (get_recursive_pixel returns black). */
+int frb_render_fern(const FrbConfig *cfg, uint32_t threads, uint64_t seed, const FrbShard *shard, uint8_t *out,
+                    size_t out_len, uint32_t format, int device);
+/* rayon::current_num_threads() as the reference would see it on this host. Host-only. */
+uint32_t frb_fern_default_threads(void);
 
 /* ---- render: device-buffer entry points (no host copies; bench `value`, GPU-resident consumers) ----- */
 

@@ -89,3 +89,56 @@ def get_image(cfg: Config, threads: int = 0) -> np.ndarray:
 
 def max_threads() -> int:
     return int(lib().oracle_max_threads())
+
+
+# ---- Barnsley fern (oracle/fern_oracle.c) --------------------------------------------------------------------------
+
+def _fern_lib():
+    L = lib()
+    if not getattr(L, "_fern_ready", False):
+        P = ctypes.POINTER
+        L.fern_oracle_chains_per_thread.restype = ctypes.c_uint32
+        L.fern_oracle_chains_per_thread.argtypes = [ctypes.c_uint32]
+        for name in ("fern_oracle_counts_chained", "fern_oracle_counts_reference_style"):
+            fn = getattr(L, name)
+            fn.restype = None
+            fn.argtypes = [P(FrbConfig), ctypes.c_uint32, ctypes.c_uint64, ctypes.c_void_p]
+        L.fern_oracle_colour_after.restype = FrbRGB
+        L.fern_oracle_colour_after.argtypes = [P(FrbConfig), ctypes.c_uint32]
+        L.fern_oracle_compose.restype = None
+        L.fern_oracle_compose.argtypes = [P(FrbConfig), ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
+        L.fern_oracle_get_image.restype = ctypes.c_uint64
+        L.fern_oracle_get_image.argtypes = [P(FrbConfig), ctypes.c_uint32, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_int]
+        L._fern_ready = True
+    return L
+
+
+def fern_counts(cfg: Config, threads: int, seed: int, reference_style: bool = False) -> np.ndarray:
+    """Hit counts (threads, H, W) uint32 of the chaos game: the CUDA path's chain decomposition, or the reference's own
+    structure (one uninterrupted orbit per thread)."""
+    c = cfg.to_c()
+    counts = np.zeros((threads, cfg.height, cfg.width), np.uint32)
+    fn = _fern_lib().fern_oracle_counts_reference_style if reference_style else _fern_lib().fern_oracle_counts_chained
+    fn(ctypes.byref(c), threads, seed & 0xFFFFFFFFFFFFFFFF, counts.ctypes.data)
+    return counts
+
+
+def fern_colour_after(cfg: Config, n: int):
+    c = cfg.to_c()
+    v = _fern_lib().fern_oracle_colour_after(ctypes.byref(c), n)
+    return (v.r, v.g, v.b)
+
+
+def fern_compose(cfg: Config, counts: np.ndarray) -> np.ndarray:
+    c = cfg.to_c()
+    counts = np.ascontiguousarray(counts, np.uint32)
+    rgb = np.empty((cfg.height, cfg.width, 3), np.uint8)
+    _fern_lib().fern_oracle_compose(ctypes.byref(c), counts.shape[0], counts.ctypes.data, rgb.ctypes.data)
+    return rgb
+
+
+def fern_get_image(cfg: Config, threads: int, seed: int, reference_style: bool = False) -> np.ndarray:
+    c = cfg.to_c()
+    rgb = np.empty((cfg.height, cfg.width, 3), np.uint8)
+    _fern_lib().fern_oracle_get_image(ctypes.byref(c), threads, seed & 0xFFFFFFFFFFFFFFFF, rgb.ctypes.data, int(reference_style))
+    return rgb
