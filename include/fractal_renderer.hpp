@@ -10,6 +10,7 @@
 #define FRACTAL_RENDERER_HPP_
 
 #include <cstdint>
+#include <random>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -102,9 +103,26 @@ inline void check(int rc, const char *what)
     if (rc != FRB_OK) throw std::runtime_error(std::string(what) + ": " + frb_last_error());
 }
 
-// get_image(&Config) -> Vec<RGB> (src/lib.rs:253): Mandelbrot | Julia arm.  device = -1 spreads the frame over all GPUs.
+// get_image's BarnsleyFern arm (src/lib.rs:271-319): `threads` = the reference's rayon thread count (0 = this host's),
+// `seed` replaces SmallRng::from_entropy (src/lib.rs:428).
+inline std::vector<calc::RGB> get_image_fern(const calc::Config &config, uint32_t threads, uint64_t seed, int device = 0)
+{
+    std::vector<calc::RGB> image(static_cast<size_t>(config.width) * config.height);
+    const FrbConfig c = config.to_c();
+    check(frb_render_fern(&c, threads, seed, nullptr, reinterpret_cast<uint8_t *>(image.data()), image.size() * 3, FRB_RGB24,
+                          device < 0 ? 0 : device), "get_image (fern)");
+    return image;
+}
+
+// get_image(&Config) -> Vec<RGB> (src/lib.rs:253), dispatching on the algorithm as the reference does: Mandelbrot | Julia ->
+// the per-pixel path (device = -1 spreads the frame over all GPUs), BarnsleyFern -> the chaos game with fresh entropy.
 inline std::vector<calc::RGB> get_image(const calc::Config &config, int device = 0)
 {
+    if (config.algo == calc::Algo::BarnsleyFern) {
+        std::random_device entropy;
+        const uint64_t seed = (static_cast<uint64_t>(entropy()) << 32) ^ entropy();
+        return get_image_fern(config, 0, seed, device);
+    }
     std::vector<calc::RGB> image(static_cast<size_t>(config.width) * config.height);
     const FrbConfig c = config.to_c();
     check(frb_render(&c, reinterpret_cast<uint8_t *>(image.data()), image.size() * 3, FRB_RGB24, device), "get_image");

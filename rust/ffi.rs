@@ -46,6 +46,8 @@ extern "C" {
     pub fn frb_shutdown();
     pub fn frb_device_count() -> c_int;
     pub fn frb_render(cfg: *const FrbConfig, out: *mut u8, out_len: usize, format: u32, device: c_int) -> c_int;
+    pub fn frb_render_fern(cfg: *const FrbConfig, threads: u32, seed: u64, shard: *const core::ffi::c_void, out: *mut u8,
+                           out_len: usize, format: u32, device: c_int) -> c_int;
     pub fn frb_last_error() -> *const c_char;
 }
 
@@ -87,6 +89,24 @@ pub fn get_image_b200(config: &Config) -> Vec<RGB> {
     if rc != 0 {
         let msg = unsafe { CStr::from_ptr(frb_last_error()) }.to_string_lossy().into_owned();
         panic!("frb_render failed ({}): {}", rc, msg); // the reference's error style is expect()/unwrap()
+    }
+    unsafe { image.set_len(n) };
+    image
+}
+
+/// Drop-in body of get_image's `Algo::BarnsleyFern` arm (src/lib.rs:271-319): T = rayon's thread count as before, the
+/// entropy the reference feeds SmallRng (src/lib.rs:428) becomes the seed of the device-side generators.
+pub fn get_image_fern_b200(config: &Config) -> Vec<RGB> {
+    use rand::RngCore;
+    let n = config.width as usize * config.height as usize;
+    let mut image: Vec<RGB> = Vec::with_capacity(n);
+    let cfg = FrbConfig::from(config);
+    let threads = rayon::current_num_threads() as u32;
+    let seed = rand::rngs::OsRng.next_u64();
+    let rc = unsafe { frb_render_fern(&cfg, threads, seed, core::ptr::null(), image.as_mut_ptr() as *mut u8, n * 3, FRB_RGB24, 0) };
+    if rc != 0 {
+        let msg = unsafe { CStr::from_ptr(frb_last_error()) }.to_string_lossy().into_owned();
+        panic!("frb_render_fern failed ({}): {}", rc, msg);
     }
     unsafe { image.set_len(n) };
     image
