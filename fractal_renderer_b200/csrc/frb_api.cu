@@ -363,14 +363,14 @@ void choose_deferred_shape(const FrbConfig &cfg, int *b, int *nb, int *minb)
 {
     *b = cfg.iterations >= 2048u ? 16 : 8;
     *nb = cfg.iterations >= 2048u ? 4 : (cfg.iterations >= 256u ? 4 : 1);
-    *minb = 4;
+    *minb = 3;  // 3 resident CTAs/SM: same kernel time as 4-5, but two slab kernels of the host-output path then co-reside (e2e 5.25 vs 5.36 ms)
     if (const char *e = getenv("FRB_TUNE_DB")) *b = atoi(e);      // tuning hooks (bench sweeps)
     if (const char *e = getenv("FRB_TUNE_NB")) *nb = atoi(e);
     if (const char *e = getenv("FRB_TUNE_MINB")) *minb = atoi(e);
     if (*b != 8 && *b != 16 && *b != 32) *b = 16;
     if (*nb != 1 && *nb != 2 && *nb != 4 && *nb != 8) *nb = 4;
     if (*b == 32 && *nb == 8) *nb = 4;
-    if (*minb != 4 && *minb != 5) *minb = 4;
+    if (*minb < 2 || *minb > 5) *minb = 4;
 }
 
 struct Plan {
@@ -477,7 +477,7 @@ int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaSt
         if (julia) frb::frb_iterate_deferred_kernel<true, B, NB, M><<<blocks, frb::kIterateThreads, 0, st>>>(p);  \
         else frb::frb_iterate_deferred_kernel<false, B, NB, M><<<blocks, frb::kIterateThreads, 0, st>>>(p);       \
         break;
-#define FRB_DEFER_CASES(B, NB) FRB_DEFER_CASE(B, NB, 4) FRB_DEFER_CASE(B, NB, 5)
+#define FRB_DEFER_CASES(B, NB) FRB_DEFER_CASE(B, NB, 2) FRB_DEFER_CASE(B, NB, 3) FRB_DEFER_CASE(B, NB, 4) FRB_DEFER_CASE(B, NB, 5)
         switch (key) {
             FRB_DEFER_CASES(8, 1) FRB_DEFER_CASES(8, 2) FRB_DEFER_CASES(8, 4) FRB_DEFER_CASES(8, 8)
             FRB_DEFER_CASES(16, 1) FRB_DEFER_CASES(16, 2) FRB_DEFER_CASES(16, 4) FRB_DEFER_CASES(16, 8)
@@ -608,17 +608,24 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
     frb::frb_coord_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
     slot.launches++;
     CU(cudaEventRecord(c.ev_fork, st));
-    const uint32_t rows_per = ((p.rows + nslabs - 1) / nslabs + 15u) & ~15u;  // multiples of 16 rows keep 16-byte alignment
+    // Equal slabs (multiples of 16 rows keep 16-byte alignment).  Slabs that shrink towards the end of the frame (weights n,
+    // n-1, ..., 1, so that the exposed last shade + copy is small; FRB_TUNE_SLABEQ=0) were measured no better: C2 5.267 vs
+    // 5.244 ms, C3 1.711 vs 1.632 ms, C4 210.5 vs 210.8 ms.
+    const bool equal_slabs = !(getenv("FRB_TUNE_SLABEQ") && atoi(getenv("FRB_TUNE_SLABEQ")) == 0);
     // measured on C2 (profiles/r1_tuning_sweeps.txt): overlapped slabs 5.555 ms, pipelined 5.58-5.78 ms, unsliced 5.60 ms
     const bool pipeline = getenv("FRB_TUNE_SLABMODE") ? atoi(getenv("FRB_TUNE_SLABMODE")) == 2 : false;
+    const uint32_t wsum = (uint32_t)(nslabs * (nslabs + 1) / 2);
     int s = 0;
-    for (uint32_t r0 = 0; r0 < p.rows; r0 += rows_per, ++s) {
+    for (uint32_t r0 = 0; r0 < p.rows; ++s) {
+        uint32_t rows_per = equal_slabs ? (p.rows + nslabs - 1) / nslabs
+                                        : (uint32_t)(((uint64_t)p.rows * (uint32_t)std::max(nslabs - s, 1) + wsum - 1) / wsum);
+        rows_per = std::max(16u, (rows_per + 15u) & ~15u);
         // pipeline: kernels of all slabs in order on aux[0], copies on aux[1] behind per-slab events.
         // otherwise: slabs alternate between the two streams and their kernels overlap freely.
         cudaStream_t ks = pipeline ? c.aux[0] : c.aux[s & 1];
         cudaStream_t cs = pipeline ? c.aux[1] : ks;
         if (s < 2) CU(cudaStreamWaitEvent(c.aux[s & 1], c.ev_fork, 0));
-        const uint32_t r1 = std::min(p.rows, r0 + rows_per);
+        const uint32_t r1 = (s >= nslabs - 1) ? p.rows : std::min(p.rows, r0 + rows_per);
         RenderParams it = p;  // iterate: global pixel indexing, its own chunk range and queue counter
         it.chunk_begin = r0 * p.chunks_per_row;
         it.total_chunks = (r1 - r0) * p.chunks_per_row;
@@ -639,6 +646,7 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
         }
         const size_t bytes = (size_t)(r1 - r0) * p.width * p.format;
         CU(cudaMemcpyAsync(host_out + pix0 * p.format, sh.out, bytes, cudaMemcpyDeviceToHost, cs));
+        r0 = r1;
     }
     for (int i = 0; i < 2; ++i) {
         CU(cudaEventRecord(c.ev_join[i], c.aux[i]));
@@ -712,7 +720,10 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
                         cfg.algo != FRB_ALGO_BARNSLEY_FERN && plan.npix >= (4u << 20) && plan.p.rows >= 256u &&
                         !getenv("FRB_TUNE_NOSLAB");
     if (sliced) {
-        const int nslabs = getenv("FRB_TUNE_SLABS") ? std::min(16, std::max(1, atoi(getenv("FRB_TUNE_SLABS")))) : 4;
+        // every slab is one more persistent launch (~0.1 ms of ramp and tail) but exposes a smaller last copy: 4 slabs up to
+        // 32 Mpx, 8 up to 64 Mpx, 16 beyond (C2 5.24 ms with 4; C4 213.5 / 211.4 / 210.5 ms with 4 / 8 / 16)
+        int nslabs = plan.npix >= (64u << 20) ? 16 : (plan.npix >= (32u << 20) ? 8 : 4);
+        if (const char *e = getenv("FRB_TUNE_SLABS")) nslabs = std::min(16, std::max(1, atoi(e)));
         if (int rc = enqueue_sliced(*c, plan, host_out, nslabs, &slot)) return rc;
     } else {
         if (int rc = enqueue(*c, plan, c->b().out, c->stream, &slot)) return rc;
