@@ -385,7 +385,7 @@ def main():
         "ms_per_frame": round(dev_ms / args.steps, 4),
         "e2e": {"value": round(e2e_value, 2), "unit": "G iter/s", "h2d_bytes_per_step": 104, "d2h_bytes_per_step": nbytes + 16,
                 "ms_per_step": round(e2e_s / args.steps * 1e3, 4),
-                "api": "frb_render_shard (what get_image binds to): config struct in, finished RGB24 frame into pinned host memory"},
+                "api": "frb_render_shard (what get_image binds to): config struct in, finished RGB24 frame into the caller's pinned host memory (written over PCIe by the streaming finisher kernel while the iterate kernel runs)"},
         "gpu_launches": launches,
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
     }

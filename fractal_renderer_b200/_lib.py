@@ -11,7 +11,7 @@ import os
 from .calc import FrbConfig
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfrb.so")
+LIB_PATH = os.environ.get("FRB_LIB_PATH") or os.path.join(_HERE, "libfrb.so")  # FRB_LIB_PATH: instrumented debug builds
 
 FRB_RGB24 = 3
 FRB_RGBA32 = 4

@@ -30,6 +30,7 @@ constexpr int kMaxDevices = 32;
 constexpr int kSlots = 64;               // in-flight async renders per device whose statistics stay readable
 constexpr uint32_t kDefaultChunk = 64;   // pixels per queue chunk
 constexpr uint32_t kDefaultBandRows = 16;
+constexpr uint32_t kMaxIterWarps = 16384;  // upper bound on resident warps of one iterate launch (SMs x CTAs/SM x 8)
 
 thread_local std::string tl_error;
 thread_local int tl_code = 0;
@@ -58,6 +59,9 @@ int fail(int code, const char *fmt, ...)
 struct StatSlot {
     unsigned long long iterations;
     unsigned long long lane_iterations;
+    unsigned long long stream_status;  // low word != 0: the streaming finisher gave up waiting (frb_stream.cuh)
+    unsigned long long reserved[9];    // device words 3..11 (trace stamps, election, work counter, generation)
+    unsigned long long stream_sticky;  // device word 12: the finisher gave up before its frame started
 };
 
 struct Slot {
@@ -92,6 +96,7 @@ struct DeviceCtx {
         uint8_t *out = nullptr;
         size_t out_cap = 0;              // bytes
         unsigned int *queue = nullptr;   // 16 chunk counters
+        uint32_t *wm = nullptr;          // kMaxIterWarps watermarks of the deferred kernel's warps (streaming finisher)
         unsigned long long *stats = nullptr;
     } sets[2];
     int cur_set = 0;
@@ -106,6 +111,7 @@ struct DeviceCtx {
     std::mutex mu;
     Slot slots[kSlots];
     uint32_t next_slot = 0;
+    uint32_t stream_gen = 0;             // generation counter of streamed frames (never 0 in a frame)
 };
 
 std::mutex g_mu;
@@ -141,6 +147,8 @@ int ctx_init(DeviceCtx *c, int dev)
         CU(cudaEventCreateWithFlags(&bs.ev_guard, cudaEventDisableTiming));
         CU(cudaMalloc(&bs.queue, 256));
         CU(cudaMalloc(&bs.stats, 256));
+        CU(cudaMemset(bs.stats, 0, 256));
+        CU(cudaMalloc(&bs.wm, kMaxIterWarps * sizeof(uint32_t)));
     }
     CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     for (auto &e : c->ev_slab) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -180,6 +188,7 @@ void ctx_destroy(DeviceCtx *c)
             cudaFree(bs.out);
             cudaFree(bs.queue);
             cudaFree(bs.stats);
+            cudaFree(bs.wm);
             if (bs.ev_guard) cudaEventDestroy(bs.ev_guard);
         }
         for (auto &s : c->slots) {
@@ -356,27 +365,37 @@ bool sparse_is_safe(const FrbConfig &cfg)
     return cmax * 1.0000001 <= 0.5 * R * R - 3.0 * R;
 }
 
-// Shape of the deferred kernel (FRB_KERNEL_DEFER6): B iterations per block, NB blocks per trip, MINB resident CTAs per SM.
+// CTA shapes of the deferred kernel: threads per CTA x resident CTAs per SM (FRB_TUNE_SHAPE picks by index).  Co-resident
+// CTAs are served very unevenly by the warp scheduler (frb_deferred.cuh), hence one wide CTA per SM by default.
+struct DeferShape {
+    int threads, per_sm;
+};
+constexpr DeferShape kDeferShapes[] = {{256, 3}, {512, 1}, {768, 1}, {1024, 1}, {512, 2}, {256, 2}};
+constexpr int kDeferShapeCount = (int)(sizeof(kDeferShapes) / sizeof(kDeferShapes[0]));
+
+// Shape of the deferred kernel (FRB_KERNEL_DEFER6): B iterations per block, NB blocks per trip, CTA shape.
 // Lanes that stop idle until the trip ends and a stopped pixel costs ~B/2 wasted + ~B/2 resolved iterations, so short
 // pixels want short blocks and trips; the iteration cap is the only a-priori hint.  Measured, profiles/r1_tuning_sweeps.txt.
 void choose_deferred_shape(const FrbConfig &cfg, int *b, int *nb, int *minb)
 {
     *b = cfg.iterations >= 2048u ? 16 : 8;
     *nb = cfg.iterations >= 2048u ? 4 : (cfg.iterations >= 256u ? 4 : 1);
-    *minb = 3;  // 3 resident CTAs/SM: same kernel time as 4-5, but two slab kernels of the host-output path then co-reside (e2e 5.25 vs 5.36 ms)
+    *minb = 2;  // index into kDeferShapes
     if (const char *e = getenv("FRB_TUNE_DB")) *b = atoi(e);      // tuning hooks (bench sweeps)
     if (const char *e = getenv("FRB_TUNE_NB")) *nb = atoi(e);
-    if (const char *e = getenv("FRB_TUNE_MINB")) *minb = atoi(e);
+    if (const char *e = getenv("FRB_TUNE_SHAPE")) *minb = atoi(e);
     if (*b != 8 && *b != 16 && *b != 32) *b = 16;
     if (*nb != 1 && *nb != 2 && *nb != 4 && *nb != 8) *nb = 4;
     if (*b == 32 && *nb == 8) *nb = 4;
-    if (*minb < 2 || *minb > 5) *minb = 4;
+    if (*b == 32 && *nb == 1) *nb = 2;
+    if (*b == 16 && *nb == 1) *nb = 2;
+    if (*minb < 0 || *minb >= kDeferShapeCount) *minb = 2;
 }
 
 struct Plan {
     RenderParams p;
     uint32_t variant;
-    int defer_b, defer_nb, defer_minb;  // deferred kernel: iterations per block, blocks per trip, resident CTAs per SM
+    int defer_b, defer_nb, defer_minb;  // deferred kernel: iterations per block, blocks per trip, CTA shape (index into kDeferShapes)
     uint64_t npix;
     size_t out_bytes;
 };
@@ -456,6 +475,15 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     return FRB_OK;
 }
 
+// CTAs of the deferred kernel for the chunks of `p` (persistent grid, never more than there are chunks for)
+uint32_t deferred_blocks(const DeviceCtx &c, const Plan &plan, const RenderParams &p)
+{
+    const DeferShape sh = kDeferShapes[plan.defer_minb];
+    const uint32_t warps_per_block = (uint32_t)sh.threads / 32;
+    const uint32_t needed = (p.total_chunks + warps_per_block - 1) / warps_per_block;
+    return std::max(1u, std::min((uint32_t)(c.sm_count * sh.per_sm), needed));
+}
+
 // Enqueues tables -> iterate -> shade (if format != 0) on `st`.  Caller holds c.mu and has set the device.
 // Launches the iteration kernel chosen by plan.variant for the chunks [p.chunk_begin, p.chunk_begin + p.total_chunks).
 int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaStream_t st)
@@ -467,23 +495,27 @@ int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaSt
     }
     const uint32_t warps_per_block = frb::kIterateThreads / 32;
     if (plan.variant == FRB_KERNEL_DEFER6) {
-        uint32_t blocks = (uint32_t)(c.sm_count * plan.defer_minb);
-        const uint32_t needed = (p.total_chunks + warps_per_block - 1) / warps_per_block;
-        blocks = std::max(1u, std::min(blocks, needed));
+        const uint32_t blocks = deferred_blocks(c, plan, p);
         const bool julia = (p.algo == FRB_ALGO_JULIA);
         const int key = plan.defer_b * 100 + plan.defer_nb * 10 + plan.defer_minb;
-#define FRB_DEFER_CASE(B, NB, M)                                                                              \
-    case (B) * 100 + (NB) * 10 + (M):                                                                        \
-        if (julia) frb::frb_iterate_deferred_kernel<true, B, NB, M><<<blocks, frb::kIterateThreads, 0, st>>>(p);  \
-        else frb::frb_iterate_deferred_kernel<false, B, NB, M><<<blocks, frb::kIterateThreads, 0, st>>>(p);       \
+#define FRB_DEFER_CASE(B, NB, S)                                                                                       \
+    case (B) * 100 + (NB) * 10 + (S):                                                                                 \
+        if (julia)                                                                                                    \
+            frb::frb_iterate_deferred_kernel<true, B, NB, kDeferShapes[S].per_sm, kDeferShapes[S].threads>            \
+                <<<blocks, kDeferShapes[S].threads, 0, st>>>(p);                                                      \
+        else                                                                                                          \
+            frb::frb_iterate_deferred_kernel<false, B, NB, kDeferShapes[S].per_sm, kDeferShapes[S].threads>           \
+                <<<blocks, kDeferShapes[S].threads, 0, st>>>(p);                                                      \
         break;
-#define FRB_DEFER_CASES(B, NB) FRB_DEFER_CASE(B, NB, 2) FRB_DEFER_CASE(B, NB, 3) FRB_DEFER_CASE(B, NB, 4) FRB_DEFER_CASE(B, NB, 5)
+#define FRB_DEFER_CASES(B, NB)                                                                                         \
+    FRB_DEFER_CASE(B, NB, 0) FRB_DEFER_CASE(B, NB, 1) FRB_DEFER_CASE(B, NB, 2) FRB_DEFER_CASE(B, NB, 3) FRB_DEFER_CASE(B, NB, 4) \
+    FRB_DEFER_CASE(B, NB, 5)
         switch (key) {
             FRB_DEFER_CASES(8, 1) FRB_DEFER_CASES(8, 2) FRB_DEFER_CASES(8, 4) FRB_DEFER_CASES(8, 8)
-            FRB_DEFER_CASES(16, 1) FRB_DEFER_CASES(16, 2) FRB_DEFER_CASES(16, 4) FRB_DEFER_CASES(16, 8)
-            FRB_DEFER_CASES(32, 1) FRB_DEFER_CASES(32, 2) FRB_DEFER_CASES(32, 4)
+            FRB_DEFER_CASES(16, 2) FRB_DEFER_CASES(16, 4) FRB_DEFER_CASES(16, 8)
+            FRB_DEFER_CASES(32, 2) FRB_DEFER_CASES(32, 4)
         default:
-            return fail(FRB_ERR_INVALID, "no deferred kernel for block %d x %d, %d CTAs/SM", plan.defer_b, plan.defer_nb, plan.defer_minb);
+            return fail(FRB_ERR_INVALID, "no deferred kernel for block %d x %d, shape %d", plan.defer_b, plan.defer_nb, plan.defer_minb);
         }
 #undef FRB_DEFER_CASES
 #undef FRB_DEFER_CASE
@@ -551,6 +583,8 @@ Slot &take_slot(DeviceCtx &c, const Plan &plan)
     slot.shaded = false;
     slot.host->iterations = 0;
     slot.host->lane_iterations = 0;
+    slot.host->stream_status = 0;
+    slot.host->stream_sticky = 0;
     return slot;
 }
 
@@ -589,6 +623,96 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
     if (plan.npix > 0) CU(cudaMemcpyAsync(slot.host, c.b().stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, st));
     CU(cudaGetLastError());
     return FRB_OK;
+}
+
+// True when a blocking host-destination render should go through the streaming finisher (frb_stream.cuh): the deferred
+// kernel, an image format and enough pixels for the second kernel to pay for itself.  FRB_TUNE_STREAM=0 disables it (the older
+// paths remain).  Device destinations (frb_render_device_async) are not streamed: there is no copy to hide, the finisher's
+// FP64 work competes with K1c's either way (measured: 4.84 ms fused shade vs 5.1-5.4 ms streamed on C2), and pipelined
+// asynchronous frames would need one set of control words per frame in flight.
+bool want_streamed(const Plan &plan)
+{
+    if (const char *e = getenv("FRB_TUNE_STREAM"))
+        if (atoi(e) == 0) return false;
+    return plan.variant == FRB_KERNEL_DEFER6 && plan.p.format != 0 && plan.npix >= (256u << 10) && plan.p.rows >= 64u;
+}
+
+// K2s on an auxiliary stream (launched first) | tables -> K1c on `st` -> join.  `dst` is the device alias of the caller's
+// pinned host buffer: the finisher writes the image over PCIe while K1c iterates.  Blocking callers only (one frame in
+// flight per device: the control words live in the device's statistics block).
+int enqueue_streamed(DeviceCtx &c, Plan &plan, uint8_t *dst, cudaStream_t st, Slot **slot_out)
+{
+    RenderParams &p = plan.p;
+    p.out = dst;
+    p.wm = c.b().wm;
+    p.records = 1u;
+    p.resolve_row0 = 0u;
+    if (++c.stream_gen == 0u) ++c.stream_gen;
+    p.stream_gen = c.stream_gen;
+    Slot &slot = take_slot(c, plan);
+    *slot_out = &slot;
+    const uint32_t blocks = deferred_blocks(c, plan, p);
+    const uint32_t nwarps = blocks * ((uint32_t)kDeferShapes[plan.defer_minb].threads / 32);
+    if (nwarps > kMaxIterWarps) return fail(FRB_ERR_INVALID, "iterate grid of %u warps exceeds the watermark table", nwarps);
+
+    frb::StreamCtl ctl;
+    memset(&ctl, 0, sizeof ctl);
+    ctl.wm = p.wm;
+    // control words live in the 64-bit statistics slots: status + minimum in stats[2] (copied back with the statistics),
+    // election + work counter in stats[10], generation in stats[11], the sticky failure flag in stats[12]
+    ctl.words = reinterpret_cast<uint32_t *>(p.stats + 2);
+    ctl.queue = reinterpret_cast<uint32_t *>(p.stats + 10);
+    ctl.gen = reinterpret_cast<const uint32_t *>(p.stats + 11);
+    ctl.sticky = reinterpret_cast<uint32_t *>(p.stats + 12);
+    ctl.gen_value = p.stream_gen;
+    ctl.gen_polls = 30u << 20;  // ~30 s: covers any frame still in flight ahead of this one
+    ctl.nwarps = nwarps;
+    // ~256 Kpx per slab: small enough that the last slab (the only exposed one) is a few microseconds of shading and copying,
+    // large enough to give every finisher CTA a block or two
+    uint32_t slab_rows = (uint32_t)std::max<uint64_t>(16u, ((256u << 10) / std::max(p.width, 1u) + 15u) & ~15u);
+    if (const char *e = getenv("FRB_TUNE_STREAMROWS")) slab_rows = (uint32_t)std::max(16, (atoi(e) + 15) & ~15);
+    ctl.slab_rows = slab_rows;
+    {
+        // bound on one wait, in polls of >= 2 us: a few seconds plus a generous allowance for the slab's own work, so that it
+        // is only ever reached if K1c stopped making progress
+        const uint64_t work = (uint64_t)slab_rows * p.width * (uint64_t)std::max(p.iterations, 1u);
+        ctl.max_polls = (uint32_t)std::min<uint64_t>((2u << 20) + (work >> 22), 0x7fffffffu);
+    }
+    int per_sm = 1;
+    if (const char *e = getenv("FRB_TUNE_STREAMCTAS")) per_sm = std::min(8, std::max(1, atoi(e)));
+    // The finisher goes first and depends on nothing (it sleeps on the generation word until K0 has run), so that its CTAs are
+    // resident before — older than — K1c's.  Frames alternate between the two auxiliary streams so that the next frame's
+    // finisher can take its seat while this frame is still running.
+    cudaStream_t fs = c.aux[p.stream_gen & 1u];
+    frb::frb_finish_stream_kernel<<<(unsigned)(c.sm_count * per_sm), frb::kShadeThreads, 0, fs>>>(p, ctl);
+    CU(cudaEventRecord(c.ev_join[p.stream_gen & 1u], fs));
+
+    if (c.b().have_guard && c.b().last_stream != st) CU(cudaStreamWaitEvent(st, c.b().ev_guard, 0));
+    CU(cudaEventRecord(slot.ev_start, st));
+    CU(cudaMemsetAsync(p.wm, 0, nwarps * sizeof(uint32_t), st));
+    const uint32_t n = std::max(p.width, p.height);
+    frb::frb_coord_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
+    if (int rc = launch_iterate(c, plan, p, st)) return rc;
+    CU(cudaEventRecord(slot.ev_iter, st));
+    CU(cudaStreamWaitEvent(st, c.ev_join[p.stream_gen & 1u], 0));
+    slot.launches += 3;
+    slot.shaded = true;
+    CU(cudaEventRecord(slot.ev_shade, st));
+    CU(cudaMemcpyAsync(slot.host, c.b().stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, st));
+    CU(cudaGetLastError());
+    return FRB_OK;
+}
+
+// Device alias of a host pointer the GPU can write (pinned / registered memory under UVA), or nullptr.
+uint8_t *device_alias_of_host(const void *host)
+{
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, host) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    if (attr.type != cudaMemoryTypeHost || attr.devicePointer == nullptr) return nullptr;
+    return static_cast<uint8_t *>(attr.devicePointer);
 }
 
 // Host-output path for large frames: the shard is cut into row slabs, each iterated + shaded + copied out on one of two
@@ -673,6 +797,8 @@ int harvest(DeviceCtx &c, Slot &slot, FrbStats *out, double total_ms)
 {
     (void)c;
     CU(cudaEventSynchronize(slot.ev_end));
+    if ((uint32_t)slot.host->stream_status != 0u || (uint32_t)slot.host->stream_sticky != 0u)
+        return fail(FRB_ERR_CUDA, "the streaming finisher gave up waiting for the iterate kernel (frb_stream.cuh: stream_wait)");
     FrbStats s = {};
     s.pixels = slot.pixels;
     s.iterations = slot.host->iterations;
@@ -719,7 +845,15 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
     const bool sliced = format != 0 && !host_iters && !host_z && plan.variant != FRB_KERNEL_SIMPLE &&
                         cfg.algo != FRB_ALGO_BARNSLEY_FERN && plan.npix >= (4u << 20) && plan.p.rows >= 256u &&
                         !getenv("FRB_TUNE_NOSLAB");
-    if (sliced) {
+    uint8_t *alias = nullptr;
+    if (format != 0 && !host_iters && !host_z && want_streamed(plan)) {
+        alias = device_alias_of_host(host_out);
+        if (alias && (reinterpret_cast<uintptr_t>(alias) & 15u) != 0) alias = nullptr;  // the shade stores are 16-byte vectors
+    }
+    if (alias) {
+        // pinned destination: the finisher writes the image into the caller's buffer while the iterate kernel runs
+        if (int rc = enqueue_streamed(*c, plan, alias, c->stream, &slot)) return rc;
+    } else if (sliced) {
         // every slab is one more persistent launch (~0.1 ms of ramp and tail) but exposes a smaller last copy: 4 slabs up to
         // 32 Mpx, 8 up to 64 Mpx, 16 beyond (C2 5.24 ms with 4; C4 213.5 / 211.4 / 210.5 ms with 4 / 8 / 16)
         int nslabs = plan.npix >= (64u << 20) ? 16 : (plan.npix >= (32u << 20) ? 8 : 4);
@@ -860,6 +994,38 @@ int frb_render_shard(const FrbConfig *cfg, const FrbShard *shard, uint8_t *out, 
     const FrbShard s = shard ? *shard : whole_frame();
     return render_blocking(*cfg, s, device, format, out, out_len, nullptr, nullptr);
 }
+
+#ifdef FRB_STREAM_TRACE
+// debug build only: globaltimer stamps of the last streamed render on `device` (see frb_stream.cuh)
+extern "C" int frb_debug_stream_times(int device, unsigned long long *out16)
+{
+    DeviceCtx *c = get_ctx(device);
+    if (!c) return tl_code;
+    CU(cudaSetDevice(device));
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(out16, c->b().stats, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    return FRB_OK;
+}
+extern "C" int frb_debug_warp_trace(unsigned int *trips, unsigned int *smid, unsigned long long *exit_ns)
+{
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpyFromSymbol(trips, frb::g_warp_trips, sizeof(unsigned int) * 16384));
+    CU(cudaMemcpyFromSymbol(smid, frb::g_warp_smid, sizeof(unsigned int) * 16384));
+    CU(cudaMemcpyFromSymbol(exit_ns, frb::g_warp_exit, sizeof(unsigned long long) * 16384));
+    return FRB_OK;
+}
+extern "C" int frb_debug_stream_trace(unsigned long long *out, unsigned int *n, int reset)
+{
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpyFromSymbol(n, frb::g_trace_n, sizeof(unsigned int)));
+    CU(cudaMemcpyFromSymbol(out, frb::g_trace, sizeof(unsigned long long) * 3 * 8192));
+    if (reset) {
+        const unsigned int z = 0;
+        CU(cudaMemcpyToSymbol(frb::g_trace_n, &z, sizeof z));
+    }
+    return FRB_OK;
+}
+#endif
 
 uint32_t frb_fern_default_threads(void)
 {

@@ -28,6 +28,12 @@
 
 namespace frb {
 
+#ifdef FRB_STREAM_TRACE
+__device__ unsigned int g_warp_trips[16384];
+__device__ unsigned int g_warp_smid[16384];
+__device__ unsigned long long g_warp_exit[16384];
+#endif
+
 constexpr uint32_t kNoPixel = 0xffffffffu;
 
 // B iterations of the 6-instruction form; nothing recorded.
@@ -82,8 +88,14 @@ __device__ __forceinline__ bool deferred_trip(double &x, double &y, double &a, d
     }
 }
 
-template <bool JULIA, int B, int NB, int MINB>
-__global__ void __launch_bounds__(kIterateThreads, MINB)
+// CT threads per CTA, MINB resident CTAs per SM.  Warps are independent workers, so the CTA shape only matters to the warp
+// scheduler — and there it matters a lot: measured on B200 (scripts/trace_warps.py), warps of co-resident CTAs are NOT served
+// evenly.  With 3 CTAs of 8 warps per SM the oldest CTA's warps made ~4000 trips per frame, the second's ~1250 and the
+// youngest's ~150: two warps per SMSP already take 3/4 of the FP64 pipe and the last CTA starves (its pixels take
+// milliseconds, which stretches the end of the frame and holds back the streaming finisher's watermarks).  Within one CTA
+// the warps progress evenly, so the default shape is ONE wide CTA per SM.
+template <bool JULIA, int B, int NB, int MINB, int CT>
+__global__ void __launch_bounds__(CT, MINB)
 frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
 {
     constexpr unsigned FULL = 0xffffffffu;
@@ -104,6 +116,12 @@ frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
     uint32_t next_chunk = 0;
     if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
     uint32_t trips = 0;  // warp-uniform
+    // Watermark for the streaming finisher (frb_stream.cuh): the lowest pixel index this warp still owes a record for.
+    // Published (release) whenever the warp fetched a chunk or the queue is drained, and as 0xffffffff on exit.  A stale
+    // value is always a lower bound: the queue hands out increasing chunk ids, so whatever the warp takes next lies above
+    // everything it holds now.
+    uint32_t *const wm = p.wm ? p.wm + (blockIdx.x * (CT / 32) + (threadIdx.x >> 5)) : nullptr;
+    bool fetched = false;
 
     for (;;) {
         // ------------------------------ service (cold) ------------------------------
@@ -141,6 +159,7 @@ frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
                                 break;
                             }
                             if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
+                            fetched = true;
                             const uint32_t cg = c + p.chunk_begin;
                             const uint32_t lr = cg / p.chunks_per_row;
                             const uint32_t seg = cg - lr * p.chunks_per_row;
@@ -178,6 +197,15 @@ frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
             }
         }
 
+        if (wm != nullptr && (fetched || drained)) {
+            uint32_t low = __reduce_min_sync(FULL, pix);  // lanes without a pixel hold kNoPixel = 0xffffffff
+            if (cur_x < cur_end) low = min(low, cur_rowpix + cur_x);
+            __threadfence();  // every lane's records before the watermark
+            __syncwarp();
+            if (lane == 0) *reinterpret_cast<volatile uint32_t *>(wm) = low;
+            fetched = false;
+        }
+
         // ------------------------------ hot ------------------------------
         // Every lane enters with at least B iterations left (host: iterations >= B).  Trips repeat until some lane stopped.
         uint32_t *const rec_iters = p.iters + pix;  // parked lanes never stop, so their (wild) addresses are never used
@@ -190,6 +218,24 @@ frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
         } while (__all_sync(FULL, live));
     }
 
+    if (wm != nullptr) {
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) *reinterpret_cast<volatile uint32_t *>(wm) = 0xffffffffu;
+#ifdef FRB_STREAM_TRACE
+        if (lane == 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            atomicMax(p.stats + 6, t);
+            const unsigned w = blockIdx.x * (CT / 32) + (threadIdx.x >> 5);
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            g_warp_trips[w] = trips;
+            g_warp_smid[w] = smid;
+            g_warp_exit[w] = t;
+        }
+#endif
+    }
     // lane-slot iterations issued: every trip is counted at its full length (a trip all of whose lanes stop early is shorter)
     if (lane == 0) atomicAdd(p.stats + 1, (unsigned long long)trips * (unsigned long long)(32 * B * NB));
 }

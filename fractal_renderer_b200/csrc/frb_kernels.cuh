@@ -58,7 +58,7 @@ struct RenderParams {
     uint32_t resolve_rows;
     uint32_t records;       // K2: 1 = iters/zfinal hold K1c's provisional records; resolve them while shading (local row 0 of the
                             // pointers is shard row resolve_row0)
-    uint32_t pad2;
+    uint32_t stream_gen;    // K0 -> K2s: generation of this frame, published once the control words are reset (0 = not streamed)
     // buffers
     double *tab_re;              // [width]   re0(x)
     double *tab_im;              // [height]  im0(y), indexed by IMAGE row
@@ -66,6 +66,7 @@ struct RenderParams {
     double2 *zfinal;             // [rows*width] position returned by recursive()
     uint8_t *out;                // [rows*width*format]
     unsigned int *queue;         // chunk counter
+    uint32_t *wm;                // K1c: per-warp watermarks for the streaming finisher (frb_stream.cuh); nullptr = not published
     unsigned long long *stats;   // [0] useful iterations, [1] lane-slot iterations issued (32 x warp trips x unroll)
 };
 
@@ -89,6 +90,18 @@ __global__ void frb_coord_tables_kernel(const __grid_constant__ RenderParams p)
     if (t == 0) {
         p.stats[0] = 0ull;
         p.stats[1] = 0ull;
+        p.stats[2] = 0ull;  // streaming finisher: status (low word), published minimum watermark (high word)
+        p.stats[10] = 0ull; //                     watcher election (low word), next work item (high word)
+        if (p.stream_gen != 0u) {
+            // the finisher of this frame is already resident (launched first, so that its CTAs are the older ones) and sleeps on
+            // this word; the watermark table was cleared by the memset that precedes this kernel in stream order
+            __threadfence();
+            *reinterpret_cast<volatile uint32_t *>(p.stats + 11) = p.stream_gen;
+        }
+#ifdef FRB_STREAM_TRACE
+        p.stats[3] = ~0ull; p.stats[4] = ~0ull; p.stats[5] = 0ull; p.stats[6] = 0ull; p.stats[7] = ~0ull;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(p.stats[8]));
+#endif
     }
     const double wf = (double)p.width, hf = (double)p.height;
     if (t < p.width) {
@@ -399,15 +412,16 @@ __device__ __forceinline__ uint32_t shade_pixel(const RenderParams &p, uint32_t 
     return 0u;
 }
 
-__global__ void __launch_bounds__(kShadeThreads)
-frb_shade_kernel(const __grid_constant__ RenderParams p)
+// Shades the 1024-pixel blocks first, first + stride, ... of the p.rows x p.width pixels the pointers of `p` address
+// (one CTA of kShadeThreads threads; `stage` = kShadeThreads * 3 words of shared memory).  Adds the loop-body executions of
+// calc::recursive (i + 1 for an escape at index i, else iterations) of the pixels it shaded to `useful`.
+__device__ __forceinline__ void shade_blocks(const RenderParams &p, uint32_t *stage, uint64_t first, uint64_t stride,
+                                             unsigned long long &useful)
 {
-    __shared__ __align__(16) uint32_t stage[kShadeThreads * 3];  // 12 B per thread for RGB24
     const uint64_t npix = (uint64_t)p.rows * p.width;
     const uint64_t cta_px = (uint64_t)kShadeThreads * kShadePxPerThread;
     const uint64_t nblocks = (npix + cta_px - 1) / cta_px;
-    unsigned long long useful = 0;  // loop-body executions of calc::recursive: i+1 for an escape at index i, else iterations
-    for (uint64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+    for (uint64_t blk = first; blk < nblocks; blk += stride) {
         const uint64_t base = blk * cta_px + (uint64_t)threadIdx.x * kShadePxPerThread;
         uint32_t c[4] = {0u, 0u, 0u, 0u};
         // position of the thread's first pixel (only needed to look up c when provisional records are resolved here)
@@ -494,10 +508,24 @@ frb_shade_kernel(const __grid_constant__ RenderParams p)
             }
         }
     }
+}
+
+// One warp-reduced atomic per warp into stats[0] (the G iter/s numerator).
+__device__ __forceinline__ void shade_publish_useful(const RenderParams &p, unsigned long long useful)
+{
     if (p.iterations == 0u || p.algo == kAlgoFern) useful = 0;
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) useful += __shfl_xor_sync(0xffffffffu, useful, s);
     if ((threadIdx.x & 31u) == 0 && useful != 0ull) atomicAdd(p.stats + 0, useful);
+}
+
+__global__ void __launch_bounds__(kShadeThreads)
+frb_shade_kernel(const __grid_constant__ RenderParams p)
+{
+    __shared__ __align__(16) uint32_t stage[kShadeThreads * 3];  // 12 B per thread for RGB24
+    unsigned long long useful = 0;
+    shade_blocks(p, stage, blockIdx.x, gridDim.x, useful);
+    shade_publish_useful(p, useful);
 }
 
 // Sum of loop-body executions when no image is shaded (frb_render_counts).
@@ -515,3 +543,5 @@ frb_sum_iterations_kernel(const __grid_constant__ RenderParams p)
 }
 
 }  // namespace frb
+
+#include "frb_stream.cuh"  // K2s: shading + copy-out streamed beside K1c

@@ -1,0 +1,111 @@
+"""The streaming finisher (csrc/frb_stream.cuh): frames shaded slab by slab BESIDE the iterate kernel and written straight into
+the caller's pinned host buffer (frb_render / frb_render_shard).  The result must be byte-identical to the other paths
+(pageable destination: iterate, then shade, then copy; device destination: frb_render_device_async) and, where the oracle
+is quick enough, within BASELINE's +-1 LSB of the oracle."""
+import ctypes
+
+import numpy as np
+import pytest
+
+import oracle_binding as ob
+from fractal_renderer_b200 import configs
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+def pinned(nbytes: int) -> np.ndarray:
+    return torch.empty(nbytes, dtype=torch.uint8).pin_memory().numpy()
+
+
+def render_ordinary(frb, cfg, fmt, shard=None):
+    """pageable destination: never streamed"""
+    sh = shard if shard is not None else frb.Shard()
+    return frb.render_shard(cfg, sh, fmt)
+
+
+def render_pinned(frb, cfg, fmt, shard=None):
+    sh = shard if shard is not None else frb.Shard()
+    rows = sh.rows(cfg.height)
+    buf = pinned(rows * cfg.width * fmt)
+    buf[:] = 0x5A
+    out = frb.render_shard(cfg, sh, fmt, out=buf.reshape(rows, cfg.width, fmt))
+    return out, frb.last_stats()
+
+
+def render_device(frb, cfg, fmt, shard=None):
+    sh = shard if shard is not None else frb.Shard()
+    rows = sh.rows(cfg.height)
+    n = rows * cfg.width * fmt
+    dev = torch.full((n + 64,), 0x5A, dtype=torch.uint8, device="cuda")
+    frb.render_device_async(cfg, dev.data_ptr(), n, fmt, device=0, shard=sh)
+    st = frb.sync_stats()
+    return dev[:n].cpu().numpy().reshape(rows, cfg.width, fmt), st
+
+
+CASES = {
+    "C1": configs.c1(),
+    "C3_2k": configs.c3().with_(width=2048, height=1536),
+    "C2_1500": configs.c2().with_(width=1500, height=1200),
+    "ragged": configs.c1().with_(width=1021, height=777, iterations=300),
+    "tall_narrow": configs.c1().with_(width=67, height=4099, iterations=200),
+    "julia_wide": configs.c3().with_(width=4096, height=80),
+}
+
+
+@pytest.mark.parametrize("fmt", [3, 4])
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_streamed_destinations_equal_the_ordinary_path(gpu, name, fmt):
+    cfg = CASES[name]
+    ref = render_ordinary(gpu, cfg, fmt)
+    ref_stats = gpu.last_stats()
+    got_h, st_h = render_pinned(gpu, cfg, fmt)
+    assert np.array_equal(got_h, ref), f"{name}: pinned host destination differs in {np.count_nonzero(got_h != ref)} bytes"
+    got_d, st_d = render_device(gpu, cfg, fmt)
+    assert np.array_equal(got_d, ref), f"{name}: device destination differs in {np.count_nonzero(got_d != ref)} bytes"
+    assert st_h["iterations"] == ref_stats["iterations"] == st_d["iterations"]
+    assert st_h["kernel_variant"] == gpu.KERNEL_DEFER6
+
+
+def test_streamed_c1_against_the_oracle(gpu):
+    cfg = configs.c1()
+    ref = ob.render_rows(cfg)
+    got, st = render_pinned(gpu, cfg, 3)
+    assert np.abs(got.astype(np.int16) - ref["rgb"].reshape(got.shape).astype(np.int16)).max() <= 1
+    assert st["iterations"] == ref["total"]
+    assert st["kernel_launches"] == 3  # tables, iterate, finisher: proof that the streamed path ran
+
+
+def test_streamed_shards_tile_the_frame(gpu):
+    cfg = configs.c1().with_(iterations=400)
+    whole = render_ordinary(gpu, cfg, 3)
+    out = np.zeros_like(whole)
+    for i in range(2):
+        sh = gpu.Shard(i, 2, 16)
+        part, _ = render_pinned(gpu, cfg, 3, shard=sh)
+        out[sh.image_rows(cfg.height)] = part
+    assert np.array_equal(out, whole)
+
+
+def test_streamed_repeatable_back_to_back(gpu):
+    """Frames reuse the watermark table and the raw buffers: a stale watermark from the previous frame must not release a
+    slab early."""
+    a = configs.c1().with_(iterations=300)
+    b = configs.c3().with_(width=1920, height=1080)
+    ra, rb = render_ordinary(gpu, a, 3), render_ordinary(gpu, b, 3)
+    for _ in range(3):
+        ga, _ = render_pinned(gpu, a, 3)
+        gb, _ = render_pinned(gpu, b, 3)
+        assert np.array_equal(ga, ra) and np.array_equal(gb, rb)
+        da, _ = render_device(gpu, a, 3)
+        assert np.array_equal(da, ra)
+
+
+def test_unaligned_pinned_destination_falls_back(gpu):
+    cfg = configs.c1().with_(iterations=200)
+    ref = render_ordinary(gpu, cfg, 3)
+    n = cfg.width * cfg.height * 3
+    buf = pinned(n + 16)[4:4 + n]  # 4-byte offset: the finisher's 16-byte stores cannot be used
+    c = cfg.to_c()
+    gpu._lib.check(gpu._lib.load().frb_render(ctypes.byref(c), buf.ctypes.data, n, 3, 0))
+    assert np.array_equal(buf.reshape(ref.shape), ref)
