@@ -61,7 +61,7 @@ struct StatSlot {
     unsigned long long lane_iterations;
     unsigned long long stream_status;  // low word != 0: the streaming finisher gave up waiting (frb_stream.cuh)
     unsigned long long reserved[9];    // device words 3..11 (trace stamps, election, work counter, generation)
-    unsigned long long stream_sticky;  // device word 12: the finisher gave up before its frame started
+    unsigned long long stream_started; // device word 12: finisher CTAs that saw their frame start (0 = nothing was shaded)
 };
 
 struct Slot {
@@ -584,7 +584,7 @@ Slot &take_slot(DeviceCtx &c, const Plan &plan)
     slot.host->iterations = 0;
     slot.host->lane_iterations = 0;
     slot.host->stream_status = 0;
-    slot.host->stream_sticky = 0;
+    slot.host->stream_started = 0;
     return slot;
 }
 
@@ -663,9 +663,10 @@ int enqueue_streamed(DeviceCtx &c, Plan &plan, uint8_t *dst, cudaStream_t st, Sl
     ctl.words = reinterpret_cast<uint32_t *>(p.stats + 2);
     ctl.queue = reinterpret_cast<uint32_t *>(p.stats + 10);
     ctl.gen = reinterpret_cast<const uint32_t *>(p.stats + 11);
-    ctl.sticky = reinterpret_cast<uint32_t *>(p.stats + 12);
+    ctl.started = reinterpret_cast<uint32_t *>(p.stats + 12);
     ctl.gen_value = p.stream_gen;
-    ctl.gen_polls = 30u << 20;  // ~30 s: covers any frame still in flight ahead of this one
+    ctl.gen_polls = 20000u;  // ~20 ms (polls of ~1 us): K0 normally follows within microseconds
+    if (const char *e = getenv("FRB_TUNE_STREAMGENPOLLS")) ctl.gen_polls = (uint32_t)std::max(0, atoi(e));  // 0: test the fallback
     ctl.nwarps = nwarps;
     // ~256 Kpx per slab: small enough that the last slab (the only exposed one) is a few microseconds of shading and copying,
     // large enough to give every finisher CTA a block or two
@@ -797,7 +798,7 @@ int harvest(DeviceCtx &c, Slot &slot, FrbStats *out, double total_ms)
 {
     (void)c;
     CU(cudaEventSynchronize(slot.ev_end));
-    if ((uint32_t)slot.host->stream_status != 0u || (uint32_t)slot.host->stream_sticky != 0u)
+    if ((uint32_t)slot.host->stream_status != 0u)
         return fail(FRB_ERR_CUDA, "the streaming finisher gave up waiting for the iterate kernel (frb_stream.cuh: stream_wait)");
     FrbStats s = {};
     s.pixels = slot.pixels;
@@ -853,6 +854,19 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
     if (alias) {
         // pinned destination: the finisher writes the image into the caller's buffer while the iterate kernel runs
         if (int rc = enqueue_streamed(*c, plan, alias, c->stream, &slot)) return rc;
+        if (int rc = finish_enqueue(*c, *slot, c->stream)) return rc;
+        CU(cudaStreamSynchronize(c->stream));
+        if ((uint32_t)slot->host->stream_started == 0u) {
+            // No finisher CTA saw the frame start (a profiler serialising kernels, or > 20 ms of other work ahead of this
+            // frame): the records are all there, shade them now with the ordinary kernel and copy the image out.
+            RenderParams sp = plan.p;
+            sp.out = c->b().out;
+            launch_shade(*c, sp, c->stream);
+            slot->launches++;
+            CU(cudaEventRecord(slot->ev_shade, c->stream));
+            CU(cudaMemcpyAsync(host_out, c->b().out, plan.out_bytes, cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaMemcpyAsync(slot->host, c->b().stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, c->stream));
+        }
     } else if (sliced) {
         // every slab is one more persistent launch (~0.1 ms of ramp and tail) but exposes a smaller last copy: 4 slabs up to
         // 32 Mpx, 8 up to 64 Mpx, 16 beyond (C2 5.24 ms with 4; C4 213.5 / 211.4 / 210.5 ms with 4 / 8 / 16)

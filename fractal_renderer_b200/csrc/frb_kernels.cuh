@@ -92,6 +92,7 @@ __global__ void frb_coord_tables_kernel(const __grid_constant__ RenderParams p)
         p.stats[1] = 0ull;
         p.stats[2] = 0ull;  // streaming finisher: status (low word), published minimum watermark (high word)
         p.stats[10] = 0ull; //                     watcher election (low word), next work item (high word)
+        p.stats[12] = 0ull; //                     finisher CTAs that saw the frame start
         if (p.stream_gen != 0u) {
             // the finisher of this frame is already resident (launched first, so that its CTAs are the older ones) and sleeps on
             // this word; the watermark table was cleared by the memset that precedes this kernel in stream order

@@ -24,7 +24,7 @@ struct StreamCtl {
     uint32_t *words;      // [0] status: 0 = ok, 1 = a wait ran out (read by the host)   [1] min over wm, refreshed by the watcher
     uint32_t *queue;      // [0] watcher election (0 = vacant, else CTA index + 1)        [1] next work item
     const uint32_t *gen;  // generation word: K0 stores gen_value there once the words above and the watermarks are reset
-    uint32_t *sticky;     // [0] set when the finisher gave up before the frame even started (never reset on the device)
+    uint32_t *started;    // [0] number of finisher CTAs that saw the frame start (reset by K0); 0 = the host must shade itself
     uint32_t gen_value;
     uint32_t gen_polls;   // bound on the wait for the generation word (polls of ~1 us)
     uint32_t nwarps;
@@ -121,7 +121,10 @@ frb_finish_stream_kernel(const __grid_constant__ RenderParams p, const __grid_co
             }
             __nanosleep(1000u);
         }
-        if (!ok) *reinterpret_cast<volatile uint32_t *>(ctl.sticky) = 1u;
+        // A CTA that never sees the frame start (kernels serialised by a profiler, or the frame held up behind other work for
+        // longer than the bound) just leaves: blocks are handed out dynamically, so the CTAs that do start shade everything,
+        // and if none does the host falls back to the ordinary shade kernel (frb_api.cu: render_blocking).
+        if (ok) atomicAdd(ctl.started, 1u);
         __threadfence();
         s_wait[0] = 0xffffffffu;
         s_item[0] = ok;

@@ -109,3 +109,15 @@ def test_unaligned_pinned_destination_falls_back(gpu):
     c = cfg.to_c()
     gpu._lib.check(gpu._lib.load().frb_render(ctypes.byref(c), buf.ctypes.data, n, 3, 0))
     assert np.array_equal(buf.reshape(ref.shape), ref)
+
+
+def test_fallback_when_the_finisher_never_sees_the_frame(gpu, monkeypatch):
+    """Under a profiler that serialises kernels (ncu) the finisher, launched first, can never see the table kernel run: it
+    leaves after its bounded wait and the host shades with the ordinary kernel.  Forced here with a zero-poll bound."""
+    cfg = configs.c1().with_(iterations=300)
+    ref = render_ordinary(gpu, cfg, 3)
+    monkeypatch.setenv("FRB_TUNE_STREAMGENPOLLS", "0")
+    got, st = render_pinned(gpu, cfg, 3)
+    assert np.array_equal(got, ref)
+    assert st["kernel_launches"] == 4  # finisher (left at once), tables, iterate, fallback shade
+    assert st["iterations"] == gpu.last_stats()["iterations"] > 0
