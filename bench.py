@@ -226,7 +226,18 @@ def main():
     if world > 1:
         import torch.distributed as dist_mod
 
-        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # NCCL may print its version banner on stdout (NCCL_DEBUG=VERSION on some boxes): keep stdout for the ONE JSON line
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
+            dist_mod.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
         dist = dist_mod
     frb.init(1 << local)
     variant = {"auto": frb.KERNEL_AUTO, "stream6": frb.KERNEL_STREAM6, "stream7": frb.KERNEL_STREAM7, "simple": frb.KERNEL_SIMPLE, "dense6": frb.KERNEL_DENSE6, "defer6": frb.KERNEL_DEFER6}[args.kernel]
