@@ -49,7 +49,7 @@ def parse():
     ap.add_argument("--workload", default="C2", choices=["C1", "C2", "C2b", "C3", "C4"])
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--kernel", default="auto", choices=["auto", "stream6", "stream7", "simple", "dense6", "defer6"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "stream6", "stream7", "simple", "dense6", "defer6", "tile"])
     return ap.parse_args()
 
 
@@ -240,7 +240,7 @@ def main():
             os.close(saved_stdout)
         dist = dist_mod
     frb.init(1 << local)
-    variant = {"auto": frb.KERNEL_AUTO, "stream6": frb.KERNEL_STREAM6, "stream7": frb.KERNEL_STREAM7, "simple": frb.KERNEL_SIMPLE, "dense6": frb.KERNEL_DENSE6, "defer6": frb.KERNEL_DEFER6}[args.kernel]
+    variant = {"auto": frb.KERNEL_AUTO, "stream6": frb.KERNEL_STREAM6, "stream7": frb.KERNEL_STREAM7, "simple": frb.KERNEL_SIMPLE, "dense6": frb.KERNEL_DENSE6, "defer6": frb.KERNEL_DEFER6, "tile": frb.KERNEL_TILE}[args.kernel]
     frb.set_kernel_variant(variant)
 
     shard = frb.Shard(rank, world, 16) if (world > 1 and args.scaling == "strong") else frb.Shard()
@@ -348,8 +348,8 @@ def main():
     per_launch_iters = my_iters / args.steps
     achieved_tflops = per_launch_iters * FLOP_PER_ITER / (it_ms * 1e-3) / 1e12
     peak_tflops = peak["dfma_per_s"] * 2 / 1e12
-    form = {frb.KERNEL_DEFER6: 6, frb.KERNEL_STREAM6: 6, frb.KERNEL_DENSE6: 6, frb.KERNEL_STREAM7: 7}.get(kernel_variant, 11)
-    kname = {frb.KERNEL_DEFER6: "frb_iterate_deferred_kernel<6>", frb.KERNEL_STREAM6: "frb_iterate_sparse_kernel<6>", frb.KERNEL_DENSE6: "frb_iterate_stream_kernel<6>",
+    form = {frb.KERNEL_TILE: 6, frb.KERNEL_DEFER6: 6, frb.KERNEL_STREAM6: 6, frb.KERNEL_DENSE6: 6, frb.KERNEL_STREAM7: 7}.get(kernel_variant, 11)
+    kname = {frb.KERNEL_TILE: "frb_iterate_tile_kernel<6> (iterate + shade)", frb.KERNEL_DEFER6: "frb_iterate_deferred_kernel<6>", frb.KERNEL_STREAM6: "frb_iterate_sparse_kernel<6>", frb.KERNEL_DENSE6: "frb_iterate_stream_kernel<6>",
              frb.KERNEL_STREAM7: "frb_iterate_stream_kernel<7>"}.get(kernel_variant, "frb_iterate_simple_kernel")
     traffic = None
     try:

@@ -22,7 +22,7 @@ from typing import Optional, Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import (FRB_RGB24, FRB_RGBA32, KERNEL_AUTO, KERNEL_DEFER6, KERNEL_DENSE6, KERNEL_NAMES, KERNEL_SIMPLE, KERNEL_STREAM6, KERNEL_STREAM7,
+from ._lib import (FRB_RGB24, FRB_RGBA32, KERNEL_AUTO, KERNEL_DEFER6, KERNEL_DENSE6, KERNEL_TILE, KERNEL_NAMES, KERNEL_SIMPLE, KERNEL_STREAM6, KERNEL_STREAM7,
                    FrbError, FrbFp64Peak, FrbShard, FrbStats)
 from .calc import RGB, Algo, Config, FrbConfig, Imaginary
 
@@ -30,7 +30,7 @@ __all__ = [
     "Algo", "Config", "Imaginary", "RGB", "FrbError", "Shard", "get_image", "get_image_rgba", "get_image_into",
     "render_shard", "render_counts", "render_frames", "render_device_async", "sync_stats", "async_stats", "last_stats",
     "device_count", "init", "shutdown", "render_fern", "fern_default_threads", "set_kernel_variant", "measure_fp64_peak", "shard_rows", "shard_row_to_y",
-    "FRB_RGB24", "FRB_RGBA32", "KERNEL_AUTO", "KERNEL_STREAM6", "KERNEL_STREAM7", "KERNEL_SIMPLE", "KERNEL_DENSE6", "KERNEL_DEFER6", "KERNEL_NAMES",
+    "FRB_RGB24", "FRB_RGBA32", "KERNEL_AUTO", "KERNEL_STREAM6", "KERNEL_STREAM7", "KERNEL_SIMPLE", "KERNEL_DENSE6", "KERNEL_DEFER6", "KERNEL_TILE", "KERNEL_NAMES",
 ]
 
 

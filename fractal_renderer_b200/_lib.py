@@ -28,7 +28,8 @@ KERNEL_STREAM7 = 2
 KERNEL_SIMPLE = 3
 KERNEL_DENSE6 = 4
 KERNEL_DEFER6 = 5
-KERNEL_NAMES = {0: "auto", 1: "stream6", 2: "stream7", 3: "simple", 4: "dense6", 5: "defer6"}
+KERNEL_TILE = 6
+KERNEL_NAMES = {0: "auto", 1: "stream6", 2: "stream7", 3: "simple", 4: "dense6", 5: "defer6", 6: "tile"}
 
 # every symbol include/frb.h declares; tests/test_abi.py checks the library exports exactly these
 EXPORTS = (

@@ -30,6 +30,7 @@ constexpr int kMaxDevices = 32;
 constexpr int kSlots = 64;               // in-flight async renders per device whose statistics stay readable
 constexpr uint32_t kDefaultChunk = 64;   // pixels per queue chunk
 constexpr uint32_t kDefaultBandRows = 16;
+constexpr uint32_t kTileMaxIterations = 384;  // iteration caps up to this take the lock-step tile kernel (frb_tile.cuh)
 constexpr uint32_t kMaxIterWarps = 16384;  // upper bound on resident warps of one iterate launch (SMs x CTAs/SM x 8)
 
 thread_local std::string tl_error;
@@ -395,6 +396,7 @@ void choose_deferred_shape(const FrbConfig &cfg, int *b, int *nb, int *minb)
 struct Plan {
     RenderParams p;
     uint32_t variant;
+    int tile_form;  // tile kernel: 6- or 7-instruction iteration
     int defer_b, defer_nb, defer_minb;  // deferred kernel: iterations per block, blocks per trip, CTA shape (index into kDeferShapes)
     uint64_t npix;
     size_t out_bytes;
@@ -449,11 +451,27 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     p.primary = (uint32_t)cfg.primary_color.r | ((uint32_t)cfg.primary_color.g << 8) | ((uint32_t)cfg.primary_color.b << 16);
     p.secondary = (uint32_t)cfg.secondary_color.r | ((uint32_t)cfg.secondary_color.g << 8) | ((uint32_t)cfg.secondary_color.b << 16);
     p.format = format;
+    // colour fast path (shade_pixel): uniform conversions done once here; FRB_TUNE_FASTSHADE=0 keeps libdevice's log2 and the
+    // division sequence (the parity tests compare the two)
+    p.iterations_d = (double)cfg.iterations;
+    p.inv_iterations = cfg.iterations ? 1.0 / p.iterations_d : 0.0;
+    p.prim_r = (double)cfg.primary_color.r;
+    p.prim_g = (double)cfg.primary_color.g;
+    p.prim_b = (double)cfg.primary_color.b;
+    p.fast_shade = (cfg.iterations >= 1u && std::isfinite(cfg.exposure) && std::fabs(cfg.exposure) < 1e290) ? 1u : 0u;
+    if (const char *e = getenv("FRB_TUNE_FASTSHADE")) p.fast_shade = (p.fast_shade && atoi(e) != 0) ? 1u : 0u;
     plan->npix = npix;
     plan->out_bytes = (size_t)npix * format;
     uint32_t v = tl_variant;
     // A forced variant is a request: outside its proven domain it is downgraded to the next kernel that is exact
     // (STREAM6 -> DENSE6 -> STREAM7); FrbStats.kernel_variant reports what actually ran.
+    // short orbits, image wanted: the lock-step tile kernel (per-pixel costs of the refill kernels outweigh their lane
+    // utilisation there; FRB_TUNE_TILEMAX moves the threshold).  It has no raw-result output: format 0 falls through.
+    uint32_t tile_max = kTileMaxIterations;
+    if (const char *e = getenv("FRB_TUNE_TILEMAX")) tile_max = (uint32_t)std::max(0, atoi(e));
+    if (v == FRB_KERNEL_TILE && (format == 0 || cfg.algo == FRB_ALGO_BARNSLEY_FERN)) v = FRB_KERNEL_AUTO;
+    if (v == FRB_KERNEL_AUTO && format != 0 && cfg.iterations <= tile_max && cfg.algo != FRB_ALGO_BARNSLEY_FERN) v = FRB_KERNEL_TILE;
+    plan->tile_form = form6_is_exact(cfg) ? 6 : 7;
     if (v == FRB_KERNEL_AUTO || v == FRB_KERNEL_DEFER6) v = sparse_is_safe(cfg) ? FRB_KERNEL_DEFER6 : FRB_KERNEL_DENSE6;
     if (v == FRB_KERNEL_STREAM6) v = sparse_is_safe(cfg) ? FRB_KERNEL_STREAM6 : FRB_KERNEL_DENSE6;
     if (v == FRB_KERNEL_DENSE6 && !form6_is_exact(cfg)) v = FRB_KERNEL_STREAM7;
@@ -491,6 +509,14 @@ int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaSt
     if (plan.variant == FRB_KERNEL_SIMPLE) {
         dim3 grid(p.rows, (p.width + 255) / 256);
         frb::frb_iterate_simple_kernel<<<grid, 256, 0, st>>>(p);
+        return FRB_OK;
+    }
+    if (plan.variant == FRB_KERNEL_TILE) {
+        // iterates AND shades: the caller skips the shade kernel
+        dim3 grid((p.width + frb::kTileW - 1) / frb::kTileW, (p.rows + frb::kTileH - 1) / frb::kTileH);
+        if (grid.y > 65535u) return fail(FRB_ERR_TOO_LARGE, "tile kernel: %u rows exceed the grid's y extent", p.rows);
+        if (plan.tile_form == 6) frb::frb_iterate_tile_kernel<6><<<grid, frb::kTileW * frb::kTileH, 0, st>>>(p);
+        else frb::frb_iterate_tile_kernel<7><<<grid, frb::kTileW * frb::kTileH, 0, st>>>(p);
         return FRB_OK;
     }
     const uint32_t warps_per_block = frb::kIterateThreads / 32;
@@ -615,8 +641,10 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
     }
     CU(cudaEventRecord(slot.ev_iter, st));
     if (plan.npix > 0) {
-        launch_shade(c, p, st);
-        slot.launches++;
+        if (plan.variant != FRB_KERNEL_TILE) {  // the tile kernel has shaded already
+            launch_shade(c, p, st);
+            slot.launches++;
+        }
         slot.shaded = (p.format != 0);
     }
     CU(cudaEventRecord(slot.ev_shade, st));
@@ -755,7 +783,6 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
         it.chunk_begin = r0 * p.chunks_per_row;
         it.total_chunks = (r1 - r0) * p.chunks_per_row;
         it.queue = c.b().queue + (s % 16);
-        if (int rc = launch_iterate(c, plan, it, ks)) return rc;
         RenderParams sh = p;  // shade: the slab's pixels through offset pointers
         const size_t pix0 = (size_t)r0 * p.width;
         sh.rows = r1 - r0;
@@ -763,8 +790,15 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
         sh.iters = p.iters + pix0;
         sh.zfinal = p.zfinal + pix0;
         sh.out = p.out + pix0 * p.format;
-        launch_shade(c, sh, ks);
-        slot.launches += 2;
+        if (plan.variant == FRB_KERNEL_TILE) {
+            // one kernel iterates and shades; it addresses the slab the way the shade kernel does
+            if (int rc = launch_iterate(c, plan, sh, ks)) return rc;
+            slot.launches += 1;
+        } else {
+            if (int rc = launch_iterate(c, plan, it, ks)) return rc;
+            launch_shade(c, sh, ks);
+            slot.launches += 2;
+        }
         if (pipeline) {
             CU(cudaEventRecord(c.ev_slab[s % 16], ks));
             CU(cudaStreamWaitEvent(cs, c.ev_slab[s % 16], 0));
@@ -843,8 +877,10 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
     }
     Slot *slot = nullptr;
     // Large RGB/RGBA frames go out in row slabs so that the device->host copy hides under the iterations.
+    // The tile kernel's frames are short (tens of microseconds a megapixel), so the copy dominates from ~0.5 Mpx on.
+    const bool tile = plan.variant == FRB_KERNEL_TILE;
     const bool sliced = format != 0 && !host_iters && !host_z && plan.variant != FRB_KERNEL_SIMPLE &&
-                        cfg.algo != FRB_ALGO_BARNSLEY_FERN && plan.npix >= (4u << 20) && plan.p.rows >= 256u &&
+                        cfg.algo != FRB_ALGO_BARNSLEY_FERN && plan.npix >= (tile ? (1u << 19) : (4u << 20)) && plan.p.rows >= 256u &&
                         !getenv("FRB_TUNE_NOSLAB");
     uint8_t *alias = nullptr;
     if (format != 0 && !host_iters && !host_z && want_streamed(plan)) {
@@ -996,7 +1032,7 @@ void frb_shutdown(void)
 
 int frb_set_kernel_variant(uint32_t variant)
 {
-    if (variant > FRB_KERNEL_DEFER6) return fail(FRB_ERR_INVALID, "unknown kernel variant %u", variant);
+    if (variant > FRB_KERNEL_TILE) return fail(FRB_ERR_INVALID, "unknown kernel variant %u", variant);
     tl_variant = variant;
     return FRB_OK;
 }

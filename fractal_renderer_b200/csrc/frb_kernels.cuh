@@ -59,6 +59,11 @@ struct RenderParams {
     uint32_t records;       // K2: 1 = iters/zfinal hold K1c's provisional records; resolve them while shading (local row 0 of the
                             // pointers is shard row resolve_row0)
     uint32_t stream_gen;    // K0 -> K2s: generation of this frame, published once the control words are reset (0 = not streamed)
+    // colour fast path (shade_pixel): uniform quantities converted once on the host instead of once per pixel
+    uint32_t fast_shade;    // 1 = exposure is finite and moderate, iterations >= 1: products of the fast path stay finite
+    double iterations_d;    // (double)iterations
+    double inv_iterations;  // RN(1 / iterations_d)
+    double prim_r, prim_g, prim_b;  // STORED fields of primary_color as doubles (the g/b swap happens in the multiply)
     // buffers
     double *tab_re;              // [width]   re0(x)
     double *tab_im;              // [height]  im0(y), indexed by IMAGE row
@@ -394,17 +399,74 @@ __device__ __forceinline__ uint32_t color_multiply(uint32_t stored, double m)
     return out_r | (out_g << 8) | (out_b << 16);
 }
 
-// get_recursive_pixel after recursive() (calc/src/lib.rs:214-234).  Returns r | g<<8 | b<<16.
-__device__ __forceinline__ uint32_t shade_pixel(const RenderParams &p, uint32_t count, double2 z)
+// ---- log2 for the smooth-colour term ----------------------------------------------------------------------------------
+// libdevice's log2(double) costs ~45 FP64-pipe instructions (denormal / special handling, a division by Newton steps,
+// compensated reconstruction); smooth colouring calls it twice per pixel plus a square root and two divisions — ~200
+// FP64 instructions a pixel, 5x the ITERATIONS of a C1 pixel.  The arguments here are tame (dist >= 2 and finite,
+// log_zn in [0.25, 256)), so: split x = 2^e * m, look up {1/c, log2 c} for the 1/128-wide interval m falls in, and
+// log2 x = e + log2 c + log2(1 + r),  r = fma(m, 1/c, -1),  |r| < 2^-8, Taylor to degree 6 (truncation < 2e-18).
+// Error <= 2.4e-16 * max(1, |log2 x|) (scripts/gen_log2_table.py builds the table; checked against long double on 4M points),
+// i.e. the same last-bit noise libdevice has against glibc/Rust — colour stays within the +-1 LSB the boundary allows, and
+// tests/test_parity_gpu.py::test_fast_shade_matches_libdevice_shade counts how rarely a byte differs at all.
+__device__ const double2 g_log2_table[128] = {
+#include "frb_log2_table.inc"
+};
+
+__device__ __forceinline__ void load_log2_table(double2 *dst)  // dst: 128 entries of shared memory; caller syncs
+{
+    for (unsigned i = threadIdx.x; i < 128u; i += blockDim.x) dst[i] = g_log2_table[i];
+}
+
+// x positive, normal, finite.
+__device__ __forceinline__ double shade_log2(double x, const double2 *tbl)
+{
+    const uint32_t hi = (uint32_t)__double2hiint(x);
+    const double m = __hiloint2double((int)((hi & 0x000fffffu) | 0x3ff00000u), __double2loint(x));
+    const double2 t = tbl[(hi >> 13) & 127u];
+    const double r = fma(m, t.x, -1.0);
+    // biased exponent -> double without a conversion instruction: the bits of 2^52 + E, minus (2^52 + 1023)
+    const double e = __dsub_rn(__hiloint2double(0x43300000, (int)(hi >> 20)), 4503599627371519.0);
+    double q = fma(r, -0.24044917348149392, 0.28853900817779266);
+    q = fma(r, q, -0.36067376022224085);
+    q = fma(r, q, 0.48089834696298783);
+    q = fma(r, q, -0.7213475204444817);
+    q = fma(r, q, 1.4426950408889634);
+    return fma(r, q, __dadd_rn(e, t.y));
+}
+
+// get_recursive_pixel after recursive() (calc/src/lib.rs:214-234).  Returns r | g<<8 | b<<16.  `lg` = the log2 table in
+// shared memory.
+__device__ __forceinline__ uint32_t shade_pixel(const RenderParams &p, uint32_t count, double2 z, const double2 *lg)
 {
     if (p.algo == kAlgoFern) return 0u;  // `_ => return RGB::BLACK`
     const double dist = __dadd_rn(__dmul_rn(z.x, z.x), __dmul_rn(z.y, z.y));
     if (dist > p.stable_limit) {
         double it = (double)count;
+        bool fast = p.fast_shade != 0u;
         if (p.smooth) {
-            const double log_zn = __ddiv_rn(log2(__dsqrt_rn(dist)), 2.0);
-            const double nu = log2(log_zn);
-            it = __dadd_rn(it, __dsub_rn(1.0, nu));
+            // 2 <= dist < inf  (high words 0x40000000 .. 0x7fefffff): both logarithms take the table path
+            if (fast && (uint32_t)__double2hiint(dist) - 0x40000000u < 0x3ff00000u) {
+                const double log_zn = __dmul_rn(shade_log2(dist, lg), 0.25);  // log2(sqrt(dist)) / 2
+                it = __dadd_rn(it, __dsub_rn(1.0, shade_log2(log_zn, lg)));
+            } else {
+                const double log_zn = __ddiv_rn(log2(__dsqrt_rn(dist)), 2.0);
+                const double nu = log2(log_zn);
+                it = __dadd_rn(it, __dsub_rn(1.0, nu));
+                fast = false;  // `it` may be infinite or NaN here
+            }
+        }
+        if (fast) {
+            // it / iterations, correctly rounded without the division sequence: q within 1 ulp, exact remainder, one
+            // correction (Markstein; needs RN(1/N), finite operands and a divisor whose mantissa is not all ones — an
+            // integer below 2^32).  Everything is finite, so the NaN checks of sat_u8 are not needed either;
+            // cvt.rzi.u32.f64 saturates negatives to 0.
+            double q = __dmul_rn(it, p.inv_iterations);
+            q = fma(fma(-q, p.iterations_d, it), p.inv_iterations, q);
+            const double mult = __dmul_rn(q, p.exposure);
+            const uint32_t out_r = min(__double2uint_rz(__dmul_rn(p.prim_r, mult)), 255u);
+            const uint32_t out_b = min(__double2uint_rz(__dmul_rn(p.prim_g, mult)), 255u);  // color_multiply's g/b swap
+            const uint32_t out_g = min(__double2uint_rz(__dmul_rn(p.prim_b, mult)), 255u);
+            return out_r | (out_g << 8) | (out_b << 16);
         }
         const double mult = __dmul_rn(__ddiv_rn(it, (double)p.iterations), p.exposure);
         return color_multiply(p.primary, mult);
@@ -414,10 +476,10 @@ __device__ __forceinline__ uint32_t shade_pixel(const RenderParams &p, uint32_t 
 }
 
 // Shades the 1024-pixel blocks first, first + stride, ... of the p.rows x p.width pixels the pointers of `p` address
-// (one CTA of kShadeThreads threads; `stage` = kShadeThreads * 3 words of shared memory).  Adds the loop-body executions of
+// (one CTA of kShadeThreads threads; `stage` = kShadeThreads * 3 words of shared memory, `lg` = the log2 table).  Adds the loop-body executions of
 // calc::recursive (i + 1 for an escape at index i, else iterations) of the pixels it shaded to `useful`.
-__device__ __forceinline__ void shade_blocks(const RenderParams &p, uint32_t *stage, uint64_t first, uint64_t stride,
-                                             unsigned long long &useful)
+__device__ __forceinline__ void shade_blocks(const RenderParams &p, uint32_t *stage, const double2 *lg, uint64_t first,
+                                             uint64_t stride, unsigned long long &useful)
 {
     const uint64_t npix = (uint64_t)p.rows * p.width;
     const uint64_t cta_px = (uint64_t)kShadeThreads * kShadePxPerThread;
@@ -453,7 +515,7 @@ __device__ __forceinline__ void shade_blocks(const RenderParams &p, uint32_t *st
                     }
                     resolve_record(p, n[k], z, cr, ci);
                 }
-                c[k] = shade_pixel(p, n[k], z);
+                c[k] = shade_pixel(p, n[k], z, lg);
                 useful += min(n[k], p.iterations - 1u) + 1u;
             }
         } else {
@@ -474,7 +536,7 @@ __device__ __forceinline__ void shade_blocks(const RenderParams &p, uint32_t *st
                         }
                         resolve_record(p, n, z, cr, ci);
                     }
-                    c[k] = shade_pixel(p, n, z);
+                    c[k] = shade_pixel(p, n, z, lg);
                     useful += min(n, p.iterations - 1u) + 1u;
                 }
         }
@@ -524,8 +586,11 @@ __global__ void __launch_bounds__(kShadeThreads)
 frb_shade_kernel(const __grid_constant__ RenderParams p)
 {
     __shared__ __align__(16) uint32_t stage[kShadeThreads * 3];  // 12 B per thread for RGB24
+    __shared__ double2 lg[128];
+    load_log2_table(lg);
+    __syncthreads();
     unsigned long long useful = 0;
-    shade_blocks(p, stage, blockIdx.x, gridDim.x, useful);
+    shade_blocks(p, stage, lg, blockIdx.x, gridDim.x, useful);
     shade_publish_useful(p, useful);
 }
 
@@ -546,3 +611,4 @@ frb_sum_iterations_kernel(const __grid_constant__ RenderParams p)
 }  // namespace frb
 
 #include "frb_stream.cuh"  // K2s: shading + copy-out streamed beside K1c
+#include "frb_tile.cuh"    // K1t: short iteration caps — lock-step tiles, colour in the same kernel

@@ -109,6 +109,8 @@ frb_finish_stream_kernel(const __grid_constant__ RenderParams p, const __grid_co
     __shared__ __align__(16) uint32_t stage[kShadeThreads * 3];
     __shared__ uint32_t s_wait[2];
     __shared__ uint32_t s_item[2];
+    __shared__ double2 lg[128];
+    load_log2_table(lg);
     if (threadIdx.x == 0) {
         // This kernel is launched BEFORE the frame's table kernel and K1c, with no dependency on them: the warp scheduler
         // favours the warps of older CTAs (frb_deferred.cuh), and the finisher — asleep most of the time, 3-4 % of the frame's
@@ -168,7 +170,7 @@ frb_finish_stream_kernel(const __grid_constant__ RenderParams p, const __grid_co
         sh.iters = p.iters + pix0;
         sh.zfinal = p.zfinal + pix0;
         sh.out = p.out + pix0 * p.format;
-        shade_blocks(sh, stage, blk, 0xffffffffffull, useful);  // exactly one block (none if blk is past a short last slab)
+        shade_blocks(sh, stage, lg, blk, 0xffffffffffull, useful);  // exactly one block (none if blk is past a short last slab)
     }
     shade_publish_useful(p, useful);
 #ifdef FRB_STREAM_TRACE

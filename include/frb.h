@@ -123,7 +123,8 @@ typedef struct FrbStats {
 } FrbStats;
 
 enum {
-    FRB_KERNEL_AUTO = 0,      /* DEFER6 when its preconditions hold (every sane input), else DENSE6, else STREAM7 */
+    FRB_KERNEL_AUTO = 0,      /* TILE for short iteration caps and image formats; else DEFER6 when its preconditions hold (every
+                                 sane input), else DENSE6, else STREAM7 */
     FRB_KERNEL_STREAM6 = 1,   /* persistent lane-refill kernel, 6 FP64 instructions / iteration, one escape filter per
                                  block of 8 iterations (needs limit >= 8 and |c| <= limit^2/2 - 3 limit: an escaped orbit
                                  then provably keeps growing) */
@@ -132,6 +133,9 @@ enum {
     FRB_KERNEL_SIMPLE = 3,    /* one thread per pixel, reference operation order as written (11 FP64 instructions), no
                                  queue: the on-GPU cross-check for the others */
     FRB_KERNEL_DENSE6 = 4,    /* as STREAM6 but with the filter every iteration (small limits, short iteration caps) */
+    FRB_KERNEL_TILE = 6,      /* image formats with an iteration cap <= 384: one thread per pixel on 8x4 tiles, filter every
+                                 iteration, colour in the same kernel (no records, no second kernel); exact for ANY input (it
+                                 takes the 7-instruction form where the 6-instruction one is not provably exact) */
     FRB_KERNEL_DEFER6 = 5     /* the default where STREAM6's preconditions hold: same arithmetic, nothing recorded in the
                                  loop; a stopped lane stores the position at the start of its last block and a resolve
                                  pass re-runs <= block+1 iterations with the reference's test after every step */

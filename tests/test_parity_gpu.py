@@ -209,3 +209,97 @@ def test_invalid_arguments(gpu):
         gpu.get_image(cfg, device=99)
     empty = gpu.get_image(cfg.with_(width=0))
     assert empty.size == 0
+
+
+# ---- the lock-step tile kernel (csrc/frb_tile.cuh): image formats with short iteration caps -----------------------------------
+
+@pytest.mark.parametrize("name", sorted(SMALL))
+def test_tile_kernel_small_cases(gpu, name):
+    """Forced on every small case (any limit, any iteration cap: it tests after every iteration, and takes the 7-instruction
+    form where the 6-instruction one is not provably exact): colour against the oracle, iteration total exact."""
+    cfg = SMALL[name]
+    ref = ob.render_rows(cfg, threads=1)
+    gpu.set_kernel_variant(gpu.KERNEL_TILE)
+    try:
+        rgb = gpu.render_shard(cfg, gpu.Shard(), gpu.FRB_RGB24)
+        st = gpu.last_stats()
+        rgba = gpu.render_shard(cfg, gpu.Shard(), gpu.FRB_RGBA32)
+    finally:
+        gpu.set_kernel_variant(gpu.KERNEL_AUTO)
+    d = np.abs(rgb.astype(np.int16) - ref["rgb"].reshape(rgb.shape).astype(np.int16))
+    assert d.max(initial=0) <= COLOUR_TOL, f"{name}: colour off by {d.max()} LSB"
+    assert np.array_equal(rgba[..., :3], rgb) and (rgba[..., 3] == 255).all()
+    if cfg.algo != 1 and cfg.width * cfg.height > 0:
+        assert st["kernel_variant"] == gpu.KERNEL_TILE
+        assert st["iterations"] == ref["total"], name
+        assert st["kernel_launches"] == 2  # tables + the tile kernel: no records, no shade kernel
+
+
+def test_tile_kernel_is_the_default_for_short_caps_and_matches_the_refill_kernel(gpu):
+    """C1 (cap 256) takes the tile kernel by default; its image is byte-identical to the deferred kernel's (same arithmetic,
+    same libdevice log2) and within 1 LSB of the oracle; longer caps keep the deferred kernel."""
+    cfg = configs.c1()
+    auto = gpu.render_shard(cfg, gpu.Shard(), gpu.FRB_RGB24)
+    st = gpu.last_stats()
+    assert st["kernel_variant"] == gpu.KERNEL_TILE
+    gpu.set_kernel_variant(gpu.KERNEL_DEFER6)
+    try:
+        other = gpu.render_shard(cfg, gpu.Shard(), gpu.FRB_RGB24)
+        st2 = gpu.last_stats()
+    finally:
+        gpu.set_kernel_variant(gpu.KERNEL_AUTO)
+    assert st2["kernel_variant"] == gpu.KERNEL_DEFER6 and st2["iterations"] == st["iterations"] == 85_781_804
+    assert np.array_equal(auto, other)
+    ref = ob.render_rows(cfg)
+    assert np.abs(auto.astype(np.int16) - ref["rgb"].reshape(auto.shape).astype(np.int16)).max() <= COLOUR_TOL
+    gpu.render_shard(configs.c1().with_(iterations=385), gpu.Shard(), gpu.FRB_RGB24)
+    assert gpu.last_stats()["kernel_variant"] == gpu.KERNEL_DEFER6
+    # shards tile, ragged sizes
+    cfg = configs.c1().with_(width=1003, height=517)
+    whole = gpu.render_shard(cfg, gpu.Shard(), gpu.FRB_RGB24)
+    out = np.zeros_like(whole)
+    for i in range(3):
+        sh = gpu.Shard(i, 3, 16)
+        out[sh.image_rows(cfg.height)] = gpu.render_shard(cfg, sh, gpu.FRB_RGB24)
+    assert np.array_equal(out, whole)
+
+
+# ---- the colour fast path (table log2, corrected reciprocal division) against the libdevice path ------------------------------
+
+def _render_both_shades(gpu, cfg, fmt):
+    import os
+    fast = gpu.render_shard(cfg, gpu.Shard(), fmt)
+    os.environ["FRB_TUNE_FASTSHADE"] = "0"
+    try:
+        slow = gpu.render_shard(cfg, gpu.Shard(), fmt)
+    finally:
+        del os.environ["FRB_TUNE_FASTSHADE"]
+    return fast, slow
+
+
+@pytest.mark.parametrize("name,cfg", [
+    ("C1", configs.c1()),
+    ("C1_it600", configs.c1().with_(iterations=600)),
+    ("julia", configs.c3().with_(width=1200, height=900)),
+    ("big_limit", configs.c1().with_(width=800, height=600, limit=1.0e4, iterations=300)),
+    ("small_limit", configs.c1().with_(width=800, height=600, limit=1.2, stable_limit=1.2, iterations=200)),
+    ("exposure", configs.c1().with_(width=800, height=600, exposure=37.5)),
+])
+def test_fast_shade_matches_libdevice_shade(gpu, name, cfg):
+    """Smooth colouring: the table log2 differs from libdevice's in the last bit or two, which moves a byte only when a
+    channel sits within ~1e-13 of an integer — allow 1 LSB on at most a handful of bytes per frame (measured: none)."""
+    fast, slow = _render_both_shades(gpu, cfg, gpu.FRB_RGB24)
+    d = np.abs(fast.astype(np.int16) - slow.astype(np.int16))
+    assert d.max() <= 1, name
+    assert int((d != 0).sum()) <= 4, f"{name}: {int((d != 0).sum())} bytes differ"
+
+
+def test_fast_shade_is_exact_without_smoothing(gpu):
+    """smooth = false: no logarithm, and the corrected reciprocal division is correctly rounded, so the fast path must be
+    byte-identical — including the structured cases where count/iterations*exposure*channel lands exactly on an integer."""
+    for it, exposure in ((50, 2.0), (255, 1.0), (100, 2.55), (256, 3.0), (1000, 10.0), (77, 0.7)):
+        cfg = configs.c1().with_(width=640, height=480, iterations=it, exposure=exposure, smooth=False)
+        fast, slow = _render_both_shades(gpu, cfg, gpu.FRB_RGBA32)
+        assert np.array_equal(fast, slow), (it, exposure)
+        ref = ob.render_rows(cfg, threads=1)
+        assert np.array_equal(fast[..., :3].reshape(-1), ref["rgb"].reshape(-1)), (it, exposure)
