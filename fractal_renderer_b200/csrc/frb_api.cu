@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -72,6 +73,7 @@ struct Slot {
     uint32_t launches = 0;
     uint32_t variant = 0;
     bool shaded = false;
+    uint64_t tile_key = 0;  // non-zero: the tile kernel was the library's choice for this frame (see tile_key_of)
 };
 
 struct DeviceCtx {
@@ -80,6 +82,10 @@ struct DeviceCtx {
     int sm_count = 0;
     int iter_blocks_per_sm[3] = {0, 0, 0};  // dense FORM 6, dense FORM 7, sparse FORM 6 (deferred: its MINB template argument)
     cudaStream_t stream = nullptr;       // the library's own stream for this device
+    // tile-kernel feedback: the scene (tile_key_of) whose last tile-kernel frame ran with poor lane utilisation, and for how
+    // many more frames the library keeps the lane-refill kernel for it before trying the tile kernel again
+    std::atomic<uint64_t> tile_bad_key{0};
+    std::atomic<uint32_t> tile_bad_frames{0};
     cudaStream_t aux[2] = {nullptr, nullptr};  // slab streams of the host-output path
     cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr}, ev_slab[16] = {};
     // Two sets of per-render device buffers: blocking and async renders use set 0; frb_render_frames alternates sets
@@ -397,10 +403,26 @@ struct Plan {
     RenderParams p;
     uint32_t variant;
     int tile_form;  // tile kernel: 6- or 7-instruction iteration
+    uint64_t tile_key;  // non-zero when AUTO chose the tile kernel
     int defer_b, defer_nb, defer_minb;  // deferred kernel: iterations per block, blocks per trip, CTA shape (index into kDeferShapes)
     uint64_t npix;
     size_t out_bytes;
 };
+
+// What "the same scene" means for the tile-kernel feedback: algorithm, cap, escape radius and the Julia constant — not the
+// view, which changes every frame of a zoom or a drag.  Never 0.
+uint64_t tile_key_of(const FrbConfig &cfg)
+{
+    uint64_t h = 0x9e3779b97f4a7c15ull;
+    const uint64_t w[5] = {cfg.algo, cfg.iterations, double_bits(cfg.limit), double_bits(cfg.julia_set.re), double_bits(cfg.julia_set.im)};
+    for (uint64_t x : w) {
+        h ^= x + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
+        h *= 0xff51afd7ed558ccdull;
+    }
+    return h | 1ull;
+}
+constexpr uint32_t kTileBackoffFrames = 64;
+constexpr double kTileMinUtilisation = 0.7;  // break-even against the refill kernel: ~0.7 at 40 iterations/px, higher above
 
 int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t format, Plan *plan)
 {
@@ -470,7 +492,19 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     uint32_t tile_max = kTileMaxIterations;
     if (const char *e = getenv("FRB_TUNE_TILEMAX")) tile_max = (uint32_t)std::max(0, atoi(e));
     if (v == FRB_KERNEL_TILE && (format == 0 || cfg.algo == FRB_ALGO_BARNSLEY_FERN)) v = FRB_KERNEL_AUTO;
-    if (v == FRB_KERNEL_AUTO && format != 0 && cfg.iterations <= tile_max && cfg.algo != FRB_ALGO_BARNSLEY_FERN) v = FRB_KERNEL_TILE;
+    plan->tile_key = 0;
+    if (v == FRB_KERNEL_AUTO && format != 0 && cfg.iterations <= tile_max && cfg.algo != FRB_ALGO_BARNSLEY_FERN) {
+        // The cap says nothing about how orbit lengths are mixed inside a tile, and lock-step warps pay for the longest lane
+        // (C3-like Julia dust: utilisation 0.38, 2.5x slower than the refill kernel).  The kernel reports its utilisation, so a
+        // scene that did badly stays with the refill kernel for the next kTileBackoffFrames frames (harvest()).
+        const uint64_t key = tile_key_of(cfg);
+        if (c.tile_bad_key.load() == key && c.tile_bad_frames.load() > 0u) {
+            c.tile_bad_frames.fetch_sub(1u);
+        } else {
+            v = FRB_KERNEL_TILE;
+            plan->tile_key = key;
+        }
+    }
     plan->tile_form = form6_is_exact(cfg) ? 6 : 7;
     if (v == FRB_KERNEL_AUTO || v == FRB_KERNEL_DEFER6) v = sparse_is_safe(cfg) ? FRB_KERNEL_DEFER6 : FRB_KERNEL_DENSE6;
     if (v == FRB_KERNEL_STREAM6) v = sparse_is_safe(cfg) ? FRB_KERNEL_STREAM6 : FRB_KERNEL_DENSE6;
@@ -607,6 +641,7 @@ Slot &take_slot(DeviceCtx &c, const Plan &plan)
     slot.launches = 0;
     slot.variant = plan.variant;
     slot.shaded = false;
+    slot.tile_key = plan.variant == FRB_KERNEL_TILE ? plan.tile_key : 0;
     slot.host->iterations = 0;
     slot.host->lane_iterations = 0;
     slot.host->stream_status = 0;
@@ -830,7 +865,6 @@ int finish_enqueue(DeviceCtx &c, Slot &slot, cudaStream_t st)
 
 int harvest(DeviceCtx &c, Slot &slot, FrbStats *out, double total_ms)
 {
-    (void)c;
     CU(cudaEventSynchronize(slot.ev_end));
     if ((uint32_t)slot.host->stream_status != 0u)
         return fail(FRB_ERR_CUDA, "the streaming finisher gave up waiting for the iterate kernel (frb_stream.cuh: stream_wait)");
@@ -838,6 +872,11 @@ int harvest(DeviceCtx &c, Slot &slot, FrbStats *out, double total_ms)
     s.pixels = slot.pixels;
     s.iterations = slot.host->iterations;
     s.lane_iterations = slot.host->lane_iterations;
+    if (slot.tile_key != 0 && slot.pixels >= (1u << 16) && s.lane_iterations > 0 &&
+        (double)s.iterations < kTileMinUtilisation * (double)s.lane_iterations) {
+        c.tile_bad_key.store(slot.tile_key);
+        c.tile_bad_frames.store(kTileBackoffFrames);
+    }
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, slot.ev_start, slot.ev_iter));
     s.iterate_ms = ms;
@@ -1034,6 +1073,10 @@ int frb_set_kernel_variant(uint32_t variant)
 {
     if (variant > FRB_KERNEL_TILE) return fail(FRB_ERR_INVALID, "unknown kernel variant %u", variant);
     tl_variant = variant;
+    // also forgets the tile-kernel feedback (make_plan / harvest), so that a caller comparing kernels starts from a known state
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (int d = 0; d < kMaxDevices; ++d)
+        if (g_ctx[d]) g_ctx[d]->tile_bad_frames.store(0u);
     return FRB_OK;
 }
 

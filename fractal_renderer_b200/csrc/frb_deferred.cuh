@@ -16,14 +16,15 @@
 // stops keeps nothing but the position it had at the START of that block (the block's input registers are still live
 // at the branch: no moves on the hot path) and its iteration index; the service code stores that pair as a
 // provisional record into iters[]/zfinal[] and refills the lane.  K1r then re-runs at most B+1 iterations per pixel
-// from the record with the reference's test after every step — at full lane efficiency, ~B/2 useful iterations per
+// (2B-1 for a pixel that ran into the iteration cap) from the record with the reference's test after every step — at full lane efficiency, ~B/2 useful iterations per
 // pixel against ~1400 in the frame — and overwrites the record with what calc::recursive returns.
 //
 // Why B+1 steps always suffice (same host-checked precondition as the sparse kernel, frb_api.cu: sparse_is_safe:
 // R = limit >= 8, |c| <= R^2/2 - 3R, S = R^2 <= 1e300): a stop by the filter means the block's last position has
 // max(re^2, im^2) >= S/2.  Either some step of the block escaped (an escaped orbit keeps growing to inf/NaN, which
 // also fire the unsigned filter, so no escape is ever missed at a block end), or the last step was a near miss and
-// the next one has |z| >= |z_prev|^2 - |c| >= 3R, which escapes.  A stop by the budget leaves < B iterations.
+// the next one has |z| >= |z_prev|^2 - |c| >= 3R, which escapes.  A stop by the budget leaves r = iterations mod B < B
+// iterations after the block just run, whose start is what the record holds: B + r <= 2B - 1 steps.
 #pragma once
 
 namespace frb {
@@ -242,7 +243,7 @@ frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
 
 // ---------------------------------------------------------------------------------------------------------
 // K1r: resolve.  One thread per pixel of the rows [p.resolve_row0, p.resolve_row0 + p.resolve_rows) of the shard:
-// reads the provisional record (iterations completed, position), runs at most p.defer_block + 1 iterations with the
+// reads the provisional record (iterations completed, position), runs at most 2 * p.defer_block - 1 iterations with the
 // reference's escape test after every step (calc/src/lib.rs:249-254, on the carried squares: same products, same
 // sum, same compare) and overwrites the record with calc::recursive's return value: (next, i) on escape,
 // (previous, iterations) otherwise.
@@ -251,7 +252,9 @@ __device__ __forceinline__ void resolve_record(const RenderParams &p, uint32_t &
 {
     const uint32_t iterations = p.iterations;
     const uint32_t done = count;
-    const uint32_t steps = min(p.defer_block + 1u, iterations - done);
+    // A stop by the filter resolves within B + 1 steps (header).  A stop by the budget happens after the block that leaves
+    // r = iterations mod B < B iterations, and the record is that block's START: B + r <= 2B - 1 steps to the cap.
+    const uint32_t steps = min(2u * p.defer_block - 1u, iterations - done);
     Orbit o = {z.x, z.y, __dmul_rn(z.x, z.x), __dmul_rn(z.y, z.y), cr, ci};
     const double S = p.limit_sq;
     const uint32_t filter_hi = p.filter_hi;

@@ -22,6 +22,14 @@ def edge_cases() -> dict[str, Config]:
         "mandel_iter7": m.with_(iterations=7),          # < unroll
         "mandel_iter8": m.with_(iterations=8),          # == unroll
         "mandel_iter9": m.with_(iterations=9),
+        # caps that are not a multiple of the deferred kernel's block (8 below 2048 iterations, 16 from there): a pixel that
+        # runs into the cap is resolved from the start of its last full block, B + (cap mod B) steps short
+        "mandel_iter15": m.with_(iterations=15),
+        "mandel_iter50": m.with_(iterations=50),
+        "mandel_iter203": m.with_(iterations=203),
+        "mandel_iter300": m.with_(iterations=300),       # 4 blocks per trip from 256 on
+        "mandel_iter2063": m.with_(iterations=2063, width=48, height=32),  # blocks of 16: cap mod 16 = 15
+        "julia_iter301": j.with_(iterations=301),
         "mandel_no_smooth": m.with_(smooth=False),
         "mandel_no_inside": m.with_(inside=False),
         "mandel_aniso_scale": m.with_(scale=Imaginary(0.3, 0.7)),

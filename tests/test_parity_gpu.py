@@ -303,3 +303,55 @@ def test_fast_shade_is_exact_without_smoothing(gpu):
         assert np.array_equal(fast, slow), (it, exposure)
         ref = ob.render_rows(cfg, threads=1)
         assert np.array_equal(fast[..., :3].reshape(-1), ref["rgb"].reshape(-1)), (it, exposure)
+
+
+def test_tile_kernel_backs_off_on_scenes_with_poor_lane_utilisation(gpu):
+    """Julia dust with a short cap: orbit lengths inside an 8x4 tile differ wildly, the lock-step kernel reports its lane
+    utilisation, and the library keeps the lane-refill kernel for the following frames of that scene (same bytes either way)."""
+    gpu.set_kernel_variant(gpu.KERNEL_AUTO)  # forgets earlier feedback
+    cfg = configs.c3().with_(width=1024, height=768, iterations=300)
+    first = gpu.render_shard(cfg, gpu.Shard(), gpu.FRB_RGB24)
+    st = gpu.last_stats()
+    assert st["kernel_variant"] == gpu.KERNEL_TILE
+    util = st["iterations"] / st["lane_iterations"]
+    assert util < 0.7, util
+    second = gpu.render_shard(cfg.with_(scale=cfg.scale), gpu.Shard(), gpu.FRB_RGB24)
+    assert gpu.last_stats()["kernel_variant"] == gpu.KERNEL_DEFER6
+    assert np.array_equal(first, second)
+    # another scene is not affected; C1 keeps the tile kernel (utilisation 0.93)
+    gpu.render_shard(configs.c1(), gpu.Shard(), gpu.FRB_RGB24)
+    st = gpu.last_stats()
+    assert st["kernel_variant"] == gpu.KERNEL_TILE and st["iterations"] / st["lane_iterations"] > 0.9
+    gpu.render_shard(configs.c1(), gpu.Shard(), gpu.FRB_RGB24)
+    assert gpu.last_stats()["kernel_variant"] == gpu.KERNEL_TILE
+    gpu.set_kernel_variant(gpu.KERNEL_AUTO)
+    gpu.render_shard(cfg, gpu.Shard(), gpu.FRB_RGB24)
+    assert gpu.last_stats()["kernel_variant"] == gpu.KERNEL_TILE  # feedback forgotten
+    gpu.set_kernel_variant(gpu.KERNEL_AUTO)
+
+
+@pytest.mark.parametrize("cap", [9, 15, 50, 257, 300, 333, 511, 2049, 2063, 4095])
+def test_deferred_kernel_caps_that_are_not_a_multiple_of_the_block(gpu, cap):
+    """Regression: a pixel that runs into the iteration cap is recorded at the start of its last full block and needs
+    B + (cap mod B) resolve steps; with B + 1 the last steps were dropped for every cap with cap mod B >= 2 (final z of
+    bounded orbits wrong, escapes in the last iterations missed).  Counts and positions against the one-thread-per-pixel
+    kernel, bit for bit, at a size where thousands of pixels reach the cap."""
+    for base in (configs.c1(), configs.c3()):
+        cfg = base.with_(width=512, height=384, iterations=cap)
+        gpu.set_kernel_variant(gpu.KERNEL_SIMPLE)
+        try:
+            ni, nz = gpu.render_counts(cfg)
+            gpu.set_kernel_variant(gpu.KERNEL_DEFER6)
+            di, dz = gpu.render_counts(cfg)
+            # below two blocks the library substitutes the dense kernel (frb_api.cu: make_plan)
+            assert gpu.last_stats()["kernel_variant"] == (gpu.KERNEL_DEFER6 if cap >= 16 else gpu.KERNEL_DENSE6)
+            img = gpu.render_shard(cfg, gpu.Shard(), gpu.FRB_RGB24)
+            gpu.set_kernel_variant(gpu.KERNEL_SIMPLE)
+            ref_img = gpu.render_shard(cfg, gpu.Shard(), gpu.FRB_RGB24)
+        finally:
+            gpu.set_kernel_variant(gpu.KERNEL_AUTO)
+        if base.algo == configs.c1().algo:
+            assert (ni == cap).sum() > 1000  # the Mandelbrot interior; the Julia set here is dust (a handful of pixels)
+        assert np.array_equal(di, ni), cap
+        assert np.array_equal(dz.view(np.uint64), nz.view(np.uint64)), cap
+        assert np.array_equal(img, ref_img), cap
