@@ -16,6 +16,10 @@ import oracle_binding as ob
 
 pytestmark = pytest.mark.gpu
 
+# FRB_DIFF_SOAK=k multiplies the number of seeds (a one-off soak: FRB_DIFF_SOAK=20 is ~5000 configurations in a few minutes)
+import os
+SOAK = max(1, int(os.environ.get("FRB_DIFF_SOAK", "1")))
+
 
 @pytest.fixture(scope="module")
 def gpu():
@@ -71,7 +75,7 @@ def random_shard(rng: np.random.Generator, gpu):
     return gpu.Shard(int(rng.integers(0, count)), count, int(rng.choice([0, 1, 8, 16, 40])))
 
 
-def check(gpu, cfg: Config, shard, fmt: int, tag: str) -> None:
+def check(gpu, cfg: Config, shard, fmt: int, tag: str, extra_destinations: bool = False) -> None:
     gpu.set_kernel_variant(gpu.KERNEL_SIMPLE)
     try:
         ni, nz = gpu.render_counts(cfg, shard)
@@ -86,11 +90,24 @@ def check(gpu, cfg: Config, shard, fmt: int, tag: str) -> None:
     assert np.array_equal(di, ni), what
     assert np.array_equal(dz.view(np.uint64), nz.view(np.uint64)), what
     assert np.array_equal(img, ref_img), what
+    if extra_destinations and ni.size:
+        # pinned host buffer (streamed beside the iterations when the frame qualifies) and device buffer
+        import torch
+        rows = ni.shape[0]
+        buf = torch.empty(rows * cfg.width * fmt, dtype=torch.uint8).pin_memory().numpy()
+        buf[:] = 0x5A
+        got = gpu.render_shard(cfg, shard, fmt, out=buf.reshape(rows, cfg.width, fmt))
+        assert np.array_equal(got, ref_img), what + f" [pinned destination, kernel {gpu.last_stats()['kernel_variant']}]"
+        dev = torch.full((buf.size + 64,), 0x5A, dtype=torch.uint8, device="cuda")
+        gpu.render_device_async(cfg, dev.data_ptr(), buf.size, fmt, device=0, shard=shard)
+        gpu.sync_stats()
+        assert np.array_equal(dev[:buf.size].cpu().numpy().reshape(ref_img.shape), ref_img), what + " [device destination]"
+        assert bool((dev[buf.size:] == 0x5A).all()), what + " [device destination overrun]"
     if cfg.iterations > 0 and ni.size:
         assert st["iterations"] == int((np.minimum(ni.astype(np.int64), cfg.iterations - 1) + 1).sum()), what
 
 
-@pytest.mark.parametrize("seed", range(16))
+@pytest.mark.parametrize("seed", range(16 * SOAK))
 def test_random_small_frames_every_kernel_agrees(gpu, seed):
     rng = np.random.default_rng(1000 + seed)
     for k in range(12):
@@ -98,13 +115,14 @@ def test_random_small_frames_every_kernel_agrees(gpu, seed):
         check(gpu, cfg, random_shard(rng, gpu), gpu.FRB_RGB24 if rng.random() < 0.5 else gpu.FRB_RGBA32, f"seed {seed} case {k}")
 
 
-@pytest.mark.parametrize("seed", range(10))
+@pytest.mark.parametrize("seed", range(10 * SOAK))
 def test_random_large_frames_every_kernel_agrees(gpu, seed):
     """Sizes at which the sliced and tile-slab host paths and multi-CTA queues are in play."""
     rng = np.random.default_rng(2000 + seed)
     for k in range(4):
         cfg = random_config(rng, big=True)
-        check(gpu, cfg, random_shard(rng, gpu), gpu.FRB_RGB24 if rng.random() < 0.5 else gpu.FRB_RGBA32, f"seed {seed} case {k}")
+        check(gpu, cfg, random_shard(rng, gpu), gpu.FRB_RGB24 if rng.random() < 0.5 else gpu.FRB_RGBA32, f"seed {seed} case {k}",
+              extra_destinations=True)
 
 
 def test_random_small_frames_against_the_cpu_oracle(gpu):
