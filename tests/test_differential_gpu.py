@@ -30,9 +30,11 @@ def gpu():
     frb.set_kernel_variant(frb.KERNEL_AUTO)
 
 
-def random_config(rng: np.random.Generator, big: bool) -> Config:
+def random_config(rng: np.random.Generator, big: bool, huge: bool = False) -> Config:
     algo = Algo.Julia if rng.random() < 0.45 else Algo.Mandelbrot
-    if big:
+    if huge:
+        w, h = int(rng.integers(2049, 2700)), int(rng.integers(2049, 2500))
+    elif big:
         w, h = int(rng.integers(300, 1400)), int(rng.integers(260, 900))
     else:
         w, h = int(rng.integers(1, 260)), int(rng.integers(1, 200))
@@ -139,3 +141,15 @@ def test_random_small_frames_against_the_cpu_oracle(gpu):
         img = gpu.render_shard(cfg, gpu.Shard(), gpu.FRB_RGB24)
         d = np.abs(img.astype(np.int16).reshape(-1) - ref["rgb"].astype(np.int16).reshape(-1))
         assert d.max(initial=0) <= 1, (k, cfg)
+
+
+@pytest.mark.parametrize("seed", range(3 * SOAK))
+def test_random_frames_above_4_megapixels_every_kernel_agrees(gpu, seed):
+    """Above 4 Mpx a pageable destination goes out in row slabs (iterate + shade + copy per slab on two streams) and the
+    tile kernel's grid spans hundreds of CTA rows; the pinned destination is streamed."""
+    rng = np.random.default_rng(3000 + seed)
+    for k in range(2):
+        cfg = random_config(rng, big=True, huge=True)
+        cfg = cfg.with_(iterations=min(cfg.iterations, 700))
+        check(gpu, cfg, random_shard(rng, gpu) if k else gpu.Shard(), gpu.FRB_RGB24 if rng.random() < 0.5 else gpu.FRB_RGBA32,
+              f"seed {seed} case {k}", extra_destinations=True)
