@@ -153,3 +153,23 @@ def test_random_frames_above_4_megapixels_every_kernel_agrees(gpu, seed):
         cfg = cfg.with_(iterations=min(cfg.iterations, 700))
         check(gpu, cfg, random_shard(rng, gpu) if k else gpu.Shard(), gpu.FRB_RGB24 if rng.random() < 0.5 else gpu.FRB_RGBA32,
               f"seed {seed} case {k}", extra_destinations=True)
+
+
+@pytest.mark.parametrize("seed", range(4 * SOAK))
+def test_random_frame_sequences_equal_frame_by_frame_renders(gpu, seed):
+    """frb_render_frames (double-buffered, alternating streams; the zoom driver's call) on random frames of different sizes
+    and kernels back to back, against one blocking reference-order render per frame."""
+    rng = np.random.default_rng(4000 + seed)
+    fmt = gpu.FRB_RGB24 if seed % 2 else gpu.FRB_RGBA32
+    frames = [random_config(rng, big=bool(k % 3 == 0)) for k in range(7)]
+    got = gpu.render_frames(frames, fmt, device=0)
+    off = 0
+    gpu.set_kernel_variant(gpu.KERNEL_SIMPLE)
+    try:
+        for k, cfg in enumerate(frames):
+            ref = gpu.render_shard(cfg, gpu.Shard(), fmt).reshape(-1)
+            assert np.array_equal(got[off:off + ref.size], ref), f"seed {seed} frame {k}: {cfg}"
+            off += ref.size
+    finally:
+        gpu.set_kernel_variant(gpu.KERNEL_AUTO)
+    assert off == got.size
