@@ -9,11 +9,13 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -783,7 +785,29 @@ uint8_t *device_alias_of_host(const void *host)
 // auxiliary streams.  The iterate kernels are persistent full-GPU grids, so slab s+1's CTAs start as slab s's CTAs
 // drain (its tail is filled) and slab s's device->host copy runs under slab s+1's iterations.  Nothing waits on
 // anything but stream order and events.  `host_out` should be pinned for the copies to be asynchronous.
-int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot **slot_out)
+// Copies the shard's local rows [r0, r1) (r0 a multiple of the band height) from `src` to the host.  band_pitch == 0: the
+// destination is the shard's own compact image.  Otherwise the destination is a whole frame in which this shard's band b starts
+// at host_out + b * band_pitch (interleaved bands of kDefaultBandRows rows, frb_render with device = -1): one strided copy for the
+// full bands, one more for a partial last band.
+int copy_rows_out(uint8_t *host_out, size_t band_pitch, const uint8_t *src, uint32_t r0, uint32_t r1, size_t row_bytes, cudaStream_t cs)
+{
+    if (r1 <= r0) return FRB_OK;
+    if (band_pitch == 0) {
+        CU(cudaMemcpyAsync(host_out + (size_t)r0 * row_bytes, src, (size_t)(r1 - r0) * row_bytes, cudaMemcpyDeviceToHost, cs));
+        return FRB_OK;
+    }
+    const size_t band_bytes = row_bytes * kDefaultBandRows;
+    const uint32_t b0 = r0 / kDefaultBandRows;
+    const uint32_t full = (r1 - r0) / kDefaultBandRows;
+    uint8_t *dst0 = host_out + (size_t)b0 * band_pitch;
+    if (full > 0) CU(cudaMemcpy2DAsync(dst0, band_pitch, src, band_bytes, band_bytes, full, cudaMemcpyDeviceToHost, cs));
+    const uint32_t rest = (r1 - r0) - full * kDefaultBandRows;
+    if (rest > 0)
+        CU(cudaMemcpyAsync(dst0 + (size_t)full * band_pitch, src + (size_t)full * band_bytes, (size_t)rest * row_bytes, cudaMemcpyDeviceToHost, cs));
+    return FRB_OK;
+}
+
+int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot **slot_out, size_t band_pitch = 0)
 {
     RenderParams &p = plan.p;
     p.out = c.b().out;
@@ -824,7 +848,7 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
         sh.resolve_row0 = r0;
         sh.iters = p.iters + pix0;
         sh.zfinal = p.zfinal + pix0;
-        sh.out = p.out + pix0 * p.format;
+        frb::offset_out(sh, p, pix0);
         if (plan.variant == FRB_KERNEL_TILE) {
             // one kernel iterates and shades; it addresses the slab the way the shade kernel does
             if (int rc = launch_iterate(c, plan, sh, ks)) return rc;
@@ -838,8 +862,7 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
             CU(cudaEventRecord(c.ev_slab[s % 16], ks));
             CU(cudaStreamWaitEvent(cs, c.ev_slab[s % 16], 0));
         }
-        const size_t bytes = (size_t)(r1 - r0) * p.width * p.format;
-        CU(cudaMemcpyAsync(host_out + pix0 * p.format, sh.out, bytes, cudaMemcpyDeviceToHost, cs));
+        if (int rc = copy_rows_out(host_out, band_pitch, sh.out, r0, r1, (size_t)p.width * p.format, cs)) return rc;
         r0 = r1;
     }
     for (int i = 0; i < 2; ++i) {
@@ -969,6 +992,78 @@ struct AsyncRecord {
 thread_local AsyncRecord tl_async_ring[kSlots];
 thread_local uint64_t tl_async_count = 0;
 
+// ---- one host worker thread per device -------------------------------------------------------------------------------------
+// frb_render(device = -1) drives every GPU of the box from one call.  Enqueued from the calling thread alone, device g's kernels
+// start ~35 us x g late (plan, ~10 launches and event records per device): at 8 GPUs the last shard of a 5 ms frame started
+// 0.28 ms after the first.  Each device therefore has a persistent worker that plans, enqueues, waits and harvests its own
+// shard; the caller runs device 0's share itself and joins the rest.  Workers are created on first use, parked on a condition
+// variable in between, and joined by frb_shutdown.
+struct DeviceWorker {
+    std::thread th;
+    std::mutex m;
+    std::condition_variable cv;
+    std::function<void()> job;
+    bool has_job = false, done = true, stop = false;
+
+    void loop()
+    {
+        std::unique_lock<std::mutex> lk(m);
+        for (;;) {
+            cv.wait(lk, [&] { return has_job || stop; });
+            if (stop) return;
+            std::function<void()> j = std::move(job);
+            has_job = false;
+            lk.unlock();
+            j();
+            lk.lock();
+            done = true;
+            cv.notify_all();
+        }
+    }
+    void submit(std::function<void()> j)
+    {
+        std::unique_lock<std::mutex> lk(m);
+        cv.wait(lk, [&] { return done; });  // one job at a time per device
+        job = std::move(j);
+        has_job = true;
+        done = false;
+        cv.notify_all();
+    }
+    void wait()
+    {
+        std::unique_lock<std::mutex> lk(m);
+        cv.wait(lk, [&] { return done; });
+    }
+};
+DeviceWorker *g_workers[kMaxDevices] = {};
+
+DeviceWorker *get_worker(int dev)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_workers[dev]) {
+        DeviceWorker *w = new DeviceWorker();
+        w->th = std::thread([w] { w->loop(); });
+        g_workers[dev] = w;
+    }
+    return g_workers[dev];
+}
+
+void stop_workers_locked()
+{
+    for (int d = 0; d < kMaxDevices; ++d) {
+        DeviceWorker *w = g_workers[d];
+        if (!w) continue;
+        {
+            std::lock_guard<std::mutex> lk(w->m);
+            w->stop = true;
+            w->cv.notify_all();
+        }
+        w->th.join();
+        delete w;
+        g_workers[d] = nullptr;
+    }
+}
+
 std::vector<int> active_devices()
 {
     std::vector<int> v;
@@ -981,6 +1076,12 @@ std::vector<int> active_devices()
     }
     for (int d = 0; d < n; ++d)
         if (mask == 0 || (mask >> d) & 1u) v.push_back(d);
+    // Test hook: FRB_TUNE_FAKE_DEVICES=k lists the first device k times, so that the multi-device paths (sharding, strided
+    // gather, per-device workers) run — shard after shard — on a box with a single GPU.
+    if (const char *e = getenv("FRB_TUNE_FAKE_DEVICES")) {
+        const int k = std::min(atoi(e), kMaxDevices);
+        if (k > 1 && !v.empty()) v.assign((size_t)k, v[0]);
+    }
     return v;
 }
 
@@ -1062,6 +1163,7 @@ int frb_init(uint32_t device_mask)
 void frb_shutdown(void)
 {
     std::lock_guard<std::mutex> lk(g_mu);
+    stop_workers_locked();
     for (int d = 0; d < kMaxDevices; ++d) {
         ctx_destroy(g_ctx[d]);
         g_ctx[d] = nullptr;
@@ -1257,47 +1359,85 @@ int frb_render(const FrbConfig *cfg, uint8_t *out, size_t out_len, uint32_t form
     const double t0 = now_ms();
     const uint32_t G = (uint32_t)devs.size();
     struct Part {
-        DeviceCtx *c;
-        Slot *slot;
-        Plan plan;
+        int rc = FRB_OK;
+        std::string err;
+        FrbStats stats = {};
     };
     std::vector<Part> parts(G);
-    std::vector<std::unique_lock<std::mutex>> locks;
-    for (uint32_t g = 0; g < G; ++g) {
-        parts[g].c = get_ctx(devs[g]);
-        if (!parts[g].c) return tl_code;
-        locks.emplace_back(parts[g].c->mu);
-    }
     const size_t row_bytes = (size_t)cfg->width * format;
-    for (uint32_t g = 0; g < G; ++g) {
-        DeviceCtx &c = *parts[g].c;
+    const uint32_t variant = tl_variant;  // the caller's kernel override travels to the workers
+    // Shard g on device devs[g]: plan, enqueue, copy out, wait, harvest.  Band b of this device lands at
+    // out + (b * G + g) * band_bytes; large shards go out slab by slab under the iterations (enqueue_sliced).
+    auto render_part = [&](uint32_t g) -> int {
+        DeviceCtx *cp = get_ctx(devs[g]);
+        if (!cp) return tl_code;
+        DeviceCtx &c = *cp;
+        std::lock_guard<std::mutex> lk(c.mu);
         CU(cudaSetDevice(c.dev));
-        FrbShard sh = {g, G, kDefaultBandRows, 0u};
-        if (int rc = make_plan(c, *cfg, sh, format, &parts[g].plan)) return rc;
-        if (int rc = ensure(c.b().out, c.b().out_cap, parts[g].plan.out_bytes + 64)) return rc;
-        if (int rc = enqueue(c, parts[g].plan, c.b().out, c.stream, &parts[g].slot)) return rc;
-        const uint32_t rows = parts[g].plan.p.rows;
-        if (rows > 0) {
-            // full bands: one strided copy; the (possibly partial) last band separately
-            const size_t band_bytes = row_bytes * kDefaultBandRows;
-            const uint32_t full = rows / kDefaultBandRows;
-            uint8_t *dst0 = out + (size_t)g * band_bytes;
-            if (full > 0)
-                CU(cudaMemcpy2DAsync(dst0, (size_t)G * band_bytes, c.b().out, band_bytes, band_bytes, full, cudaMemcpyDeviceToHost, c.stream));
-            const uint32_t rest = rows - full * kDefaultBandRows;
-            if (rest > 0)
-                CU(cudaMemcpyAsync(dst0 + (size_t)full * G * band_bytes, c.b().out + (size_t)full * band_bytes, (size_t)rest * row_bytes,
-                                   cudaMemcpyDeviceToHost, c.stream));
+        Plan plan;
+        const FrbShard sh = {g, G, kDefaultBandRows, 0u};
+        if (int rc = make_plan(c, *cfg, sh, format, &plan)) return rc;
+        if (int rc = ensure(c.b().out, c.b().out_cap, plan.out_bytes + 64)) return rc;
+        const size_t band_bytes = row_bytes * kDefaultBandRows;
+        uint8_t *dst0 = out + (size_t)g * band_bytes;
+        const bool tile = plan.variant == FRB_KERNEL_TILE;
+        const bool sliced = plan.variant != FRB_KERNEL_SIMPLE && plan.npix >= (tile ? (1u << 19) : (4u << 20)) && plan.p.rows >= 256u &&
+                            !getenv("FRB_TUNE_NOSLAB");
+        Slot *slot = nullptr;
+        // Pinned destination: the streaming finisher writes this shard's bands straight into the caller's frame (strided output
+        // addressing, RenderParams::out_band_q) while the iterate kernel runs — no device image, no copy.
+        uint8_t *alias = nullptr;
+        if (want_streamed(plan) && row_bytes < (1ull << 32)) {
+            alias = device_alias_of_host(out);
+            if (alias && (reinterpret_cast<uintptr_t>(alias) & 15u) != 0) alias = nullptr;
         }
-        if (int rc = finish_enqueue(c, *parts[g].slot, c.stream)) return rc;
+        if (alias) {
+            plan.p.out_band_q = (uint32_t)(band_bytes >> 4);
+            plan.p.out_band_gap = (unsigned long long)(G - 1) * band_bytes;
+            plan.p.out_off = 0;
+            if (int rc = enqueue_streamed(c, plan, alias + (size_t)g * band_bytes, c.stream, &slot)) return rc;
+            if (int rc = finish_enqueue(c, *slot, c.stream)) return rc;
+            CU(cudaStreamSynchronize(c.stream));
+            if ((uint32_t)slot->host->stream_started == 0u) {
+                // no finisher CTA saw the frame start (render_blocking has the same fallback): shade compactly, copy out
+                RenderParams sp = plan.p;
+                sp.out = c.b().out;
+                sp.out_band_q = 0u;
+                sp.out_off = 0;
+                launch_shade(c, sp, c.stream);
+                slot->launches++;
+                CU(cudaEventRecord(slot->ev_shade, c.stream));
+                if (int rc = copy_rows_out(dst0, (size_t)G * band_bytes, c.b().out, 0u, plan.p.rows, row_bytes, c.stream)) return rc;
+                CU(cudaMemcpyAsync(slot->host, c.b().stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, c.stream));
+            }
+        } else if (sliced) {
+            int nslabs = plan.npix >= (64u << 20) ? 16 : (plan.npix >= (32u << 20) ? 8 : 4);
+            if (const char *e = getenv("FRB_TUNE_SLABS")) nslabs = std::min(16, std::max(1, atoi(e)));
+            if (int rc = enqueue_sliced(c, plan, dst0, nslabs, &slot, (size_t)G * band_bytes)) return rc;
+        } else {
+            if (int rc = enqueue(c, plan, c.b().out, c.stream, &slot)) return rc;
+            if (int rc = copy_rows_out(dst0, (size_t)G * band_bytes, c.b().out, 0u, plan.p.rows, row_bytes, c.stream)) return rc;
+        }
+        if (int rc = finish_enqueue(c, *slot, c.stream)) return rc;
+        CU(cudaStreamSynchronize(c.stream));
+        return harvest(c, *slot, &parts[g].stats, 0.0);
+    };
+    auto run_part = [&](uint32_t g) {
+        tl_variant = variant;
+        parts[g].rc = render_part(g);
+        if (parts[g].rc != FRB_OK) parts[g].err = tl_error;
+    };
+    std::vector<DeviceWorker *> workers(G, nullptr);
+    for (uint32_t g = 1; g < G; ++g) {
+        workers[g] = get_worker(devs[g]);
+        workers[g]->submit([&run_part, g] { run_part(g); });
     }
+    run_part(0);
+    for (uint32_t g = 1; g < G; ++g) workers[g]->wait();
     FrbStats total = {};
     for (uint32_t g = 0; g < G; ++g) {
-        DeviceCtx &c = *parts[g].c;
-        CU(cudaSetDevice(c.dev));
-        CU(cudaStreamSynchronize(c.stream));
-        FrbStats s;
-        if (int rc = harvest(c, *parts[g].slot, &s, 0.0)) return rc;
+        if (parts[g].rc != FRB_OK) return fail(parts[g].rc, "device %d: %s", devs[g], parts[g].err.c_str());
+        const FrbStats &s = parts[g].stats;
         total.pixels += s.pixels;
         total.iterations += s.iterations;
         total.lane_iterations += s.lane_iterations;

@@ -59,6 +59,13 @@ struct RenderParams {
     uint32_t records;       // K2: 1 = iters/zfinal hold K1c's provisional records; resolve them while shading (local row 0 of the
                             // pointers is shard row resolve_row0)
     uint32_t stream_gen;    // K0 -> K2s: generation of this frame, published once the control words are reset (0 = not streamed)
+    // Output addressing of K2 / K2s.  out_band_q == 0: `out` is this launch's own compact image.  Otherwise `out` is where the
+    // shard's band 0 starts inside a WHOLE frame shared with other devices' shards (frb_render, device = -1): compact byte offset
+    // o of the shard maps to o + (o / band_bytes) * out_band_gap, band_bytes = 16 * out_band_q (one band of kDefaultBandRows rows),
+    // and out_off is the compact offset of this launch's first pixel (row slabs are launches of their own).
+    uint32_t out_band_q;    // band_bytes / 16 (bands are multiples of 16 bytes: 16 rows)
+    unsigned long long out_band_gap;  // bytes between the end of a band and the shard's next band = (G - 1) * band_bytes
+    unsigned long long out_off;
     // colour fast path (shade_pixel): uniform quantities converted once on the host instead of once per pixel
     uint32_t fast_shade;    // 1 = exposure is finite and moderate, iterations >= 1: products of the fast path stay finite
     double iterations_d;    // (double)iterations
@@ -74,6 +81,23 @@ struct RenderParams {
     uint32_t *wm;                // K1c: per-warp watermarks for the streaming finisher (frb_stream.cuh); nullptr = not published
     unsigned long long *stats;   // [0] useful iterations, [1] lane-slot iterations issued (32 x warp trips x unroll)
 };
+
+// Address of compact byte offset `off` of this launch's image (see RenderParams::out_band_q).  Stores of up to 16 bytes at
+// 16-byte-aligned offsets never straddle a band: bands are multiples of 16 bytes.
+__device__ __forceinline__ uint8_t *out_ptr(const RenderParams &p, unsigned long long off)
+{
+    if (p.out_band_q == 0u) return p.out + off;
+    const unsigned long long o = p.out_off + off;
+    const uint32_t band = (uint32_t)(o >> 4) / p.out_band_q;  // o < 2^36 (2^32 pixels x 4 B, frb_api.cu: make_plan)
+    return p.out + o + (unsigned long long)band * p.out_band_gap;
+}
+
+// The launch parameters of the sub-image starting at compact pixel pix0 (row slabs): its output begins there.
+__host__ __device__ inline void offset_out(RenderParams &sub, const RenderParams &p, size_t pix0)
+{
+    if (p.out_band_q != 0u) sub.out_off = p.out_off + (unsigned long long)pix0 * p.format;
+    else sub.out = p.out + pix0 * p.format;
+}
 
 // local (compact) row of a shard -> image row; see FrbShard in include/frb.h
 __device__ __forceinline__ uint32_t local_row_to_y(const RenderParams &p, uint32_t lr)
@@ -544,10 +568,10 @@ __device__ __forceinline__ void shade_blocks(const RenderParams &p, uint32_t *st
         if (p.format == 4u) {
             if (base + 4 <= npix) {
                 uint4 v = make_uint4(c[0] | 0xff000000u, c[1] | 0xff000000u, c[2] | 0xff000000u, c[3] | 0xff000000u);
-                *reinterpret_cast<uint4 *>(p.out + base * 4) = v;
+                *reinterpret_cast<uint4 *>(out_ptr(p, base * 4)) = v;
             } else {
                 for (int k = 0; k < 4; ++k)
-                    if (base + k < npix) reinterpret_cast<uint32_t *>(p.out)[base + k] = c[k] | 0xff000000u;
+                    if (base + k < npix) *reinterpret_cast<uint32_t *>(out_ptr(p, (base + k) * 4)) = c[k] | 0xff000000u;
             }
         } else {
             // pack 4 px (12 B) as three words: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
@@ -560,14 +584,13 @@ __device__ __forceinline__ void shade_blocks(const RenderParams &p, uint32_t *st
                 stage[threadIdx.x * 3 + 2] = w2;
                 __syncthreads();
                 // 256 threads x 12 B = 3072 B = 192 x 16 B
-                uint4 *dst = reinterpret_cast<uint4 *>(p.out + blk * cta_px * 3);
-                if (threadIdx.x < (kShadeThreads * 3) / 4) dst[threadIdx.x] = reinterpret_cast<const uint4 *>(stage)[threadIdx.x];
+                if (threadIdx.x < (kShadeThreads * 3) / 4)
+                    *reinterpret_cast<uint4 *>(out_ptr(p, blk * cta_px * 3 + threadIdx.x * 16u)) = reinterpret_cast<const uint4 *>(stage)[threadIdx.x];
                 __syncthreads();
             } else {
-                uint8_t *dst = p.out + base * 3;
                 const uint32_t w[3] = {w0, w1, w2};
                 for (int k = 0; k < 12; ++k)
-                    if (base * 3 + k < npix * 3) dst[k] = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
+                    if (base * 3 + k < npix * 3) *out_ptr(p, base * 3 + k) = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
             }
         }
     }

@@ -169,7 +169,7 @@ frb_finish_stream_kernel(const __grid_constant__ RenderParams p, const __grid_co
         sh.resolve_row0 = p.resolve_row0 + r0;
         sh.iters = p.iters + pix0;
         sh.zfinal = p.zfinal + pix0;
-        sh.out = p.out + pix0 * p.format;
+        offset_out(sh, p, pix0);
         shade_blocks(sh, stage, lg, blk, 0xffffffffffull, useful);  // exactly one block (none if blk is past a short last slab)
     }
     shade_publish_useful(p, useful);
