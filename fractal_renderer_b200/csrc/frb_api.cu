@@ -86,6 +86,7 @@ struct DeviceCtx {
     cudaStream_t stream = nullptr;       // the library's own stream for this device
     // tile-kernel feedback: the scene (tile_key_of) whose last tile-kernel frame ran with poor lane utilisation, and for how
     // many more frames the library keeps the lane-refill kernel for it before trying the tile kernel again
+    std::vector<const void *> loaded_kernels;  // preload_kernel(): kernels whose code is known to be on the device
     std::atomic<uint64_t> tile_bad_key{0};
     std::atomic<uint32_t> tile_bad_frames{0};
     cudaStream_t aux[2] = {nullptr, nullptr};  // slab streams of the host-output path
@@ -538,6 +539,45 @@ uint32_t deferred_blocks(const DeviceCtx &c, const Plan &plan, const RenderParam
     return std::max(1u, std::min((uint32_t)(c.sm_count * sh.per_sm), needed));
 }
 
+// The instantiation of the deferred kernel a plan selects (nullptr: none compiled for that combination).
+const void *deferred_kernel_of(const Plan &plan, bool julia)
+{
+    const int key = plan.defer_b * 100 + plan.defer_nb * 10 + plan.defer_minb;
+#define FRB_DEFER_CASE(B, NB, S)                                                                                                   \
+    case (B) * 100 + (NB) * 10 + (S):                                                                                             \
+        return julia ? (const void *)frb::frb_iterate_deferred_kernel<true, B, NB, kDeferShapes[S].per_sm, kDeferShapes[S].threads> \
+                     : (const void *)frb::frb_iterate_deferred_kernel<false, B, NB, kDeferShapes[S].per_sm, kDeferShapes[S].threads>;
+#define FRB_DEFER_CASES(B, NB)                                                                                         \
+    FRB_DEFER_CASE(B, NB, 0) FRB_DEFER_CASE(B, NB, 1) FRB_DEFER_CASE(B, NB, 2) FRB_DEFER_CASE(B, NB, 3) FRB_DEFER_CASE(B, NB, 4) \
+    FRB_DEFER_CASE(B, NB, 5)
+    switch (key) {
+        FRB_DEFER_CASES(8, 1) FRB_DEFER_CASES(8, 2) FRB_DEFER_CASES(8, 4) FRB_DEFER_CASES(8, 8)
+        FRB_DEFER_CASES(16, 2) FRB_DEFER_CASES(16, 4) FRB_DEFER_CASES(16, 8)
+        FRB_DEFER_CASES(32, 2) FRB_DEFER_CASES(32, 4)
+    default:
+        return nullptr;
+    }
+#undef FRB_DEFER_CASES
+#undef FRB_DEFER_CASE
+}
+
+// CUDA loads a kernel's code on its first launch (lazy module loading), and that load waits for the kernels already running
+// on the device.  The streaming finisher is launched FIRST and then sleeps until the frame's table kernel has run — so a table
+// or iterate kernel that still has to be loaded at that point cannot start until the finisher gives up: 20 ms and the fallback
+// path if it is the table kernel, a 4 s stall and an error if it is the iterate kernel (seen on the first streamed frame of
+// each algorithm / block shape in a process).  Everything that is launched while a finisher may be resident is therefore
+// loaded beforehand: cudaFuncGetAttributes forces the load.
+int preload_kernel(DeviceCtx &c, const void *kfn)
+{
+    if (!kfn) return FRB_OK;
+    for (const void *k : c.loaded_kernels)
+        if (k == kfn) return FRB_OK;
+    cudaFuncAttributes attr;
+    CU(cudaFuncGetAttributes(&attr, kfn));
+    c.loaded_kernels.push_back(kfn);
+    return FRB_OK;
+}
+
 // Enqueues tables -> iterate -> shade (if format != 0) on `st`.  Caller holds c.mu and has set the device.
 // Launches the iteration kernel chosen by plan.variant for the chunks [p.chunk_begin, p.chunk_begin + p.total_chunks).
 int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaStream_t st)
@@ -559,28 +599,11 @@ int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaSt
     if (plan.variant == FRB_KERNEL_DEFER6) {
         const uint32_t blocks = deferred_blocks(c, plan, p);
         const bool julia = (p.algo == FRB_ALGO_JULIA);
-        const int key = plan.defer_b * 100 + plan.defer_nb * 10 + plan.defer_minb;
-#define FRB_DEFER_CASE(B, NB, S)                                                                                       \
-    case (B) * 100 + (NB) * 10 + (S):                                                                                 \
-        if (julia)                                                                                                    \
-            frb::frb_iterate_deferred_kernel<true, B, NB, kDeferShapes[S].per_sm, kDeferShapes[S].threads>            \
-                <<<blocks, kDeferShapes[S].threads, 0, st>>>(p);                                                      \
-        else                                                                                                          \
-            frb::frb_iterate_deferred_kernel<false, B, NB, kDeferShapes[S].per_sm, kDeferShapes[S].threads>           \
-                <<<blocks, kDeferShapes[S].threads, 0, st>>>(p);                                                      \
-        break;
-#define FRB_DEFER_CASES(B, NB)                                                                                         \
-    FRB_DEFER_CASE(B, NB, 0) FRB_DEFER_CASE(B, NB, 1) FRB_DEFER_CASE(B, NB, 2) FRB_DEFER_CASE(B, NB, 3) FRB_DEFER_CASE(B, NB, 4) \
-    FRB_DEFER_CASE(B, NB, 5)
-        switch (key) {
-            FRB_DEFER_CASES(8, 1) FRB_DEFER_CASES(8, 2) FRB_DEFER_CASES(8, 4) FRB_DEFER_CASES(8, 8)
-            FRB_DEFER_CASES(16, 2) FRB_DEFER_CASES(16, 4) FRB_DEFER_CASES(16, 8)
-            FRB_DEFER_CASES(32, 2) FRB_DEFER_CASES(32, 4)
-        default:
+        const void *kfn = deferred_kernel_of(plan, julia);
+        if (!kfn)
             return fail(FRB_ERR_INVALID, "no deferred kernel for block %d x %d, shape %d", plan.defer_b, plan.defer_nb, plan.defer_minb);
-        }
-#undef FRB_DEFER_CASES
-#undef FRB_DEFER_CASE
+        void *args[] = {const_cast<RenderParams *>(&p)};
+        CU(cudaLaunchKernel(kfn, dim3(blocks), dim3((unsigned)kDeferShapes[plan.defer_minb].threads), args, 0, st));
         // raw-result path: K1r over the rows this launch covered (with an image format the shade kernel resolves instead)
         RenderParams r = p;
         r.resolve_row0 = p.chunks_per_row ? p.chunk_begin / p.chunks_per_row : 0u;
@@ -749,13 +772,18 @@ int enqueue_streamed(DeviceCtx &c, Plan &plan, uint8_t *dst, cudaStream_t st, Sl
     // The finisher goes first and depends on nothing (it sleeps on the generation word until K0 has run), so that its CTAs are
     // resident before — older than — K1c's.  Frames alternate between the two auxiliary streams so that the next frame's
     // finisher can take its seat while this frame is still running.
+    if (int rc = preload_kernel(c, (const void *)frb::frb_coord_tables_kernel)) return rc;
+    if (int rc = preload_kernel(c, deferred_kernel_of(plan, p.algo == FRB_ALGO_JULIA))) return rc;
+    if (int rc = preload_kernel(c, (const void *)frb::frb_finish_stream_kernel)) return rc;
+    // (the watermark reset goes ahead of the finisher too: whatever a memset needs is then in place before anything sleeps on
+    // the device; the finisher does not look at the table before K0, which follows the reset on `st`, has published the frame)
+    if (c.b().have_guard && c.b().last_stream != st) CU(cudaStreamWaitEvent(st, c.b().ev_guard, 0));
+    CU(cudaEventRecord(slot.ev_start, st));
+    CU(cudaMemsetAsync(p.wm, 0, nwarps * sizeof(uint32_t), st));
     cudaStream_t fs = c.aux[p.stream_gen & 1u];
     frb::frb_finish_stream_kernel<<<(unsigned)(c.sm_count * per_sm), frb::kShadeThreads, 0, fs>>>(p, ctl);
     CU(cudaEventRecord(c.ev_join[p.stream_gen & 1u], fs));
 
-    if (c.b().have_guard && c.b().last_stream != st) CU(cudaStreamWaitEvent(st, c.b().ev_guard, 0));
-    CU(cudaEventRecord(slot.ev_start, st));
-    CU(cudaMemsetAsync(p.wm, 0, nwarps * sizeof(uint32_t), st));
     const uint32_t n = std::max(p.width, p.height);
     frb::frb_coord_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
     if (int rc = launch_iterate(c, plan, p, st)) return rc;

@@ -121,3 +121,32 @@ def test_fallback_when_the_finisher_never_sees_the_frame(gpu, monkeypatch):
     assert np.array_equal(got, ref)
     assert st["kernel_launches"] == 4  # finisher (left at once), tables, iterate, fallback shade
     assert st["iterations"] == gpu.last_stats()["iterations"] > 0
+
+
+def test_first_streamed_frame_of_each_kernel_instance_in_a_fresh_process():
+    """Regression: CUDA loads a kernel on its first launch and the load waits for running kernels — the finisher, launched
+    first, is one.  A fresh process whose FIRST call of each algorithm / block shape is a streamed frame used to stall 4 s and
+    fail.  Runs in a subprocess because every other test has long loaded the kernels."""
+    import subprocess
+    import sys
+    code = r'''
+import sys, time, torch, numpy as np
+sys.path.insert(0, ".")
+import fractal_renderer_b200 as frb
+from fractal_renderer_b200 import configs
+for name, cfg in (("mandel_b16", configs.c2().with_(width=1500, height=1200)), ("julia_b8", configs.c3().with_(width=2048, height=1536)),
+                  ("mandel_b8", configs.c1().with_(iterations=600)), ("julia_b16", configs.c3().with_(width=1024, height=768, iterations=3000))):
+    buf = torch.empty(cfg.width * cfg.height * 3, dtype=torch.uint8).pin_memory().numpy()
+    t = time.perf_counter()
+    frb.get_image_into(cfg, buf, frb.FRB_RGB24, device=0)
+    dt = time.perf_counter() - t
+    st = frb.last_stats()
+    assert dt < 1.0, (name, dt)
+    assert st["kernel_launches"] == 3, (name, st)   # finisher + tables + iterate: streamed, no fallback
+    ref = np.empty_like(buf)
+    frb.set_kernel_variant(frb.KERNEL_SIMPLE); frb.get_image_into(cfg, ref, frb.FRB_RGB24, device=0); frb.set_kernel_variant(frb.KERNEL_AUTO)
+    assert np.array_equal(buf, ref), name
+print("ok")
+'''
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
