@@ -157,7 +157,10 @@ int frb_set_kernel_variant(uint32_t variant);
 /* ---- render: host-buffer entry points (what the reference's get_image binds to) ---------------------- */
 
 /* Renders the whole frame on device `device` (-1 = spread over all initialised devices by interleaved
- * 16-row bands) and writes width*height*format bytes into the HOST buffer `out` (out_len >= that).
+ * 16-row bands, one host worker thread per device) and writes width*height*format bytes into the HOST
+ * buffer `out` (out_len >= that).  Any host memory works; if `out` is pinned (cudaHostAlloc /
+ * cudaHostRegister, 16-byte aligned) the image is written into it over PCIe while the iterations run —
+ * by every device into its own bands when device = -1 — instead of being copied afterwards.
  * Replaces get_image's Mandelbrot|Julia arm (src/lib.rs:255-269). */
 int frb_render(const FrbConfig *cfg, uint8_t *out, size_t out_len, uint32_t format, int device);
 
