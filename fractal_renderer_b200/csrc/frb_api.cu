@@ -1179,8 +1179,26 @@ int frb_init(uint32_t device_mask)
     bool any = false;
     for (int d = 0; d < n; ++d) {
         if (device_mask != 0 && !((device_mask >> d) & 1u)) continue;
-        if (!get_ctx(d)) return tl_code;
+        DeviceCtx *c = get_ctx(d);
+        if (!c) return tl_code;
         any = true;
+        // load the code of the kernels an ordinary frame launches (CUDA would otherwise do it at their first launch, tens of
+        // milliseconds into the first render): tables, shade, finisher, tile, and the default shapes of the deferred kernel
+        std::lock_guard<std::mutex> lk(c->mu);
+        CU(cudaSetDevice(d));
+        const void *common[] = {(const void *)frb::frb_coord_tables_kernel, (const void *)frb::frb_shade_kernel,
+                                (const void *)frb::frb_finish_stream_kernel, (const void *)frb::frb_iterate_tile_kernel<6>,
+                                (const void *)frb::frb_resolve_kernel, (const void *)frb::frb_sum_iterations_kernel};
+        for (const void *k : common)
+            if (int rc = preload_kernel(*c, k)) return rc;
+        for (uint32_t it : {64u, 1000u, 4000u})
+            for (int julia = 0; julia < 2; ++julia) {
+                FrbConfig probe = {};
+                probe.iterations = it;
+                Plan pl = {};
+                choose_deferred_shape(probe, &pl.defer_b, &pl.defer_nb, &pl.defer_minb);
+                if (int rc = preload_kernel(*c, deferred_kernel_of(pl, julia != 0))) return rc;
+            }
     }
     if (!any) return fail(FRB_ERR_INVALID, "device mask 0x%x selects none of the %d devices", device_mask, n);
     std::lock_guard<std::mutex> lk(g_mu);

@@ -150,3 +150,29 @@ print("ok")
 '''
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_init_loads_the_kernels_of_an_ordinary_frame():
+    """frb_init promises that the first render is not charged for set-up: after it, the first (streamed) frame of a fresh
+    process runs at frame speed, not at module-loading speed."""
+    import subprocess
+    import sys
+    code = r'''
+import sys, time, torch
+sys.path.insert(0, ".")
+import fractal_renderer_b200 as frb
+from fractal_renderer_b200 import configs
+cfg = configs.c2().with_(width=1500, height=1200)
+buf = torch.empty(cfg.width * cfg.height * 3, dtype=torch.uint8).pin_memory().numpy()
+frb.init()
+t = time.perf_counter()
+frb.get_image_into(cfg, buf, frb.FRB_RGB24, device=0)
+dt = time.perf_counter() - t
+st = frb.last_stats()
+print("first frame ms", round(dt * 1e3, 2), st["kernel_launches"])
+assert st["kernel_launches"] == 3
+assert dt < 0.5, dt
+print("ok")
+'''
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
