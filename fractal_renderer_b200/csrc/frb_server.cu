@@ -8,15 +8,67 @@
 // the coalescing logic is tested on machines without a GPU.
 #include "../../include/frb.h"
 
+#include <cuda_runtime.h>
+
 #include <condition_variable>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
 #include <string>
 #include <thread>
+#include <utility>
 #include <vector>
 
 namespace {
+
+// A grow-only frame buffer.  With the library's own renderer the frames are PINNED host memory, so frb_render writes them over
+// PCIe while the iterations run (streaming finisher) or copies them at DMA speed instead of through the driver's staging
+// buffers; with an injected renderer (tests without a GPU) or if pinning fails it is ordinary memory.
+struct FrameBuf {
+    uint8_t *p = nullptr;
+    size_t cap = 0;
+    bool pinned = false;
+    FrameBuf() = default;
+    FrameBuf(const FrameBuf &) = delete;
+    FrameBuf &operator=(const FrameBuf &) = delete;
+    ~FrameBuf() { release(); }
+    void release()
+    {
+        if (p) {
+            if (pinned) cudaFreeHost(p);
+            else free(p);
+        }
+        p = nullptr;
+        cap = 0;
+    }
+    bool reserve(size_t n, bool want_pinned)
+    {
+        if (n <= cap) return true;
+        release();
+        const size_t want = n + n / 8 + 4096;  // head-room: interactive resizes should not re-pin every frame
+        if (want_pinned) {
+            void *q = nullptr;
+            if (cudaHostAlloc(&q, want, cudaHostAllocPortable) == cudaSuccess) {
+                p = static_cast<uint8_t *>(q);
+                pinned = true;
+                cap = want;
+                return true;
+            }
+            cudaGetLastError();
+        }
+        p = static_cast<uint8_t *>(malloc(want));
+        pinned = false;
+        cap = p ? want : 0;
+        return p != nullptr;
+    }
+    void swap(FrameBuf &o)
+    {
+        std::swap(p, o.p);
+        std::swap(cap, o.cap);
+        std::swap(pinned, o.pinned);
+    }
+};
 
 struct Server {
     int device = 0;
@@ -34,7 +86,8 @@ struct Server {
     bool have_request = false;         // the mpsc channel holds at most one config here
     FrbConfig request = {};
     // the shared `image: Arc<Mutex<Option<ColorImage>>>`
-    std::vector<uint8_t> image;
+    FrameBuf image;
+    bool pin_frames = false;           // the library's own renderer: frames in pinned memory
     uint32_t image_w = 0, image_h = 0;
     bool image_fresh = false;
     uint64_t frames_rendered = 0, requests = 0, coalesced = 0;
@@ -51,7 +104,7 @@ int default_renderer(const FrbConfig *cfg, uint8_t *rgba, size_t len, void *user
 
 void render_loop(Server *s)
 {
-    std::vector<uint8_t> frame;
+    FrameBuf frame;
     for (;;) {
         FrbConfig cfg;
         {
@@ -62,8 +115,12 @@ void render_loop(Server *s)
             s->have_request = false;
         }
         const size_t bytes = (size_t)cfg.width * cfg.height * 4;
-        frame.resize(bytes);
-        const int rc = s->renderer(&cfg, frame.data(), bytes, s->user);
+        int rc = FRB_OK;
+        if (!frame.reserve(bytes, s->pin_frames)) {
+            rc = FRB_ERR_INVALID;
+        } else {
+            rc = s->renderer(&cfg, frame.p, bytes, s->user);
+        }
         {
             std::lock_guard<std::mutex> lk(s->mu);
             s->last_rc = rc;
@@ -74,7 +131,7 @@ void render_loop(Server *s)
                 s->image_fresh = true;
                 s->frames_rendered++;
             } else {
-                s->last_error = frb_last_error();
+                s->last_error = frame.p ? frb_last_error() : "out of host memory for the frame";
             }
             s->working = false;
         }
@@ -108,6 +165,7 @@ FrbServer *frb_server_create(int device, FrbServerRenderFn renderer, void *user)
     if (!s) return nullptr;
     s->device = device;
     s->renderer = renderer ? renderer : default_renderer;
+    s->pin_frames = renderer == nullptr;
     s->user = renderer ? user : (void *)(intptr_t)device;
     s->thread = std::thread(render_loop, s);
     return reinterpret_cast<FrbServer *>(s);
@@ -160,7 +218,7 @@ int frb_server_poll(FrbServer *h, uint8_t *rgba, size_t len, uint32_t *width, ui
     if (height) *height = s->image_h;
     if (!rgba) return 1;  // peek: report the size, leave the frame in the slot
     if (len < bytes) return FRB_ERR_INVALID;
-    memcpy(rgba, s->image.data(), bytes);
+    memcpy(rgba, s->image.p, bytes);
     s->image_fresh = false;
     if (s->try_redraw) request_locked(s);
     return 1;

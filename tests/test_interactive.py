@@ -101,3 +101,17 @@ def test_frame_server_renders_rgba_on_gpu(gpu):
         frame2 = srv.poll(10000)
         assert frame2 is not None and np.array_equal(frame2, gpu.get_image_rgba(view.config))
         assert not np.array_equal(frame2, frame)
+
+
+@pytest.mark.gpu
+def test_frame_server_frames_are_streamed_into_pinned_memory(gpu):
+    """The server's own frames are pinned, so frames large enough for it take the streaming finisher (3 launches: finisher,
+    tables, iterate) — and resizing up and down between requests keeps working on the grow-only buffers."""
+    big = configs.c1().with_(width=1280, height=720, iterations=600)
+    small = configs.c3().with_(width=640, height=360)
+    with FrameServer(device=0) as srv:
+        for cfg in (big, small, big, big.with_(width=1920, height=1080)):
+            srv.request(cfg)
+            frame = srv.poll(10000)
+            assert frame is not None and frame.shape[:2] == (cfg.height, cfg.width)
+            assert np.array_equal(frame, gpu.get_image_rgba(cfg)), (cfg.width, cfg.height)
