@@ -30,7 +30,7 @@ __all__ = [
     "Algo", "Config", "Imaginary", "RGB", "FrbError", "Shard", "get_image", "get_image_rgba", "get_image_into",
     "render_shard", "render_counts", "render_frames", "render_device_async", "sync_stats", "async_stats", "last_stats",
     "device_count", "init", "shutdown", "render_fern", "fern_default_threads", "set_kernel_variant", "measure_fp64_peak", "shard_rows", "shard_row_to_y",
-    "FRB_RGB24", "FRB_RGBA32", "KERNEL_AUTO", "KERNEL_STREAM6", "KERNEL_STREAM7", "KERNEL_SIMPLE", "KERNEL_DENSE6", "KERNEL_DEFER6", "KERNEL_TILE", "KERNEL_NAMES",
+    "FRB_RGB24", "FRB_RGBA32", "pinned_empty", "KERNEL_AUTO", "KERNEL_STREAM6", "KERNEL_STREAM7", "KERNEL_SIMPLE", "KERNEL_DENSE6", "KERNEL_DEFER6", "KERNEL_TILE", "KERNEL_NAMES",
 ]
 
 
@@ -102,6 +102,20 @@ def get_image_into(config: Config, out: np.ndarray, fmt: int = FRB_RGB24, device
     c = config.to_c()
     _lib.check(_lib.load().frb_render(ctypes.byref(c), out.ctypes.data, out.nbytes, fmt, device))
     return out
+
+
+def pinned_empty(nbytes: int) -> np.ndarray:
+    """A uint8 array in page-locked host memory (frb_host_alloc): as the destination of get_image_into / render_shard it is
+    written by the GPU while the iterations run instead of being copied afterwards.  Freed when the array is collected."""
+    import weakref
+    lib = _lib.load()
+    ptr = lib.frb_host_alloc(max(int(nbytes), 1))
+    if not ptr:
+        raise _lib.FrbError(_lib.FRB_ERR_CUDA, lib.frb_last_error().decode("utf-8", "replace"))
+    raw = (ctypes.c_uint8 * max(int(nbytes), 1)).from_address(ptr)
+    arr = np.frombuffer(raw, dtype=np.uint8, count=int(nbytes))
+    weakref.finalize(raw, lib.frb_host_free, ptr)  # `arr` keeps `raw` alive through its base
+    return arr
 
 
 def get_image(config: Config, device: int = 0) -> np.ndarray:

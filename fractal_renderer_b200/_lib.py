@@ -54,6 +54,10 @@ EXPORTS = (
     "frb_last_error",
     "frb_last_stats",
     "frb_measure_fp64_peak",
+    "frb_host_alloc",
+    "frb_host_free",
+    "frb_host_register",
+    "frb_host_unregister",
     "frb_server_create",
     "frb_server_destroy",
     "frb_server_request",
@@ -167,6 +171,14 @@ def load() -> ctypes.CDLL:
     L.frb_last_error.argtypes = []
     L.frb_last_stats.restype = ctypes.c_int
     L.frb_last_stats.argtypes = [P(FrbStats)]
+    L.frb_host_alloc.restype = ctypes.c_void_p
+    L.frb_host_alloc.argtypes = [ctypes.c_size_t]
+    L.frb_host_free.restype = None
+    L.frb_host_free.argtypes = [ctypes.c_void_p]
+    L.frb_host_register.restype = ctypes.c_int
+    L.frb_host_register.argtypes = [ctypes.c_void_p, ctypes.c_size_t]
+    L.frb_host_unregister.restype = ctypes.c_int
+    L.frb_host_unregister.argtypes = [ctypes.c_void_p]
     L.frb_measure_fp64_peak.restype = ctypes.c_int
     L.frb_measure_fp64_peak.argtypes = [ctypes.c_int, P(FrbFp64Peak)]
     L.frb_server_create.restype = ctypes.c_void_p

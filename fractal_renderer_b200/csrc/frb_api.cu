@@ -1121,6 +1121,42 @@ extern "C" {
 
 uint32_t frb_abi_version(void) { return FRB_ABI_VERSION; }
 
+void *frb_host_alloc(size_t bytes)
+{
+    if (frb_device_count() == 0) {
+        fail(FRB_ERR_NO_DEVICE, "no usable CUDA device: pinned memory needs the driver");
+        return nullptr;
+    }
+    void *p = nullptr;
+    const cudaError_t e = cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        fail(FRB_ERR_CUDA, "cudaHostAlloc(%zu bytes): %s", bytes, cudaGetErrorString(e));
+        return nullptr;
+    }
+    return p;
+}
+
+void frb_host_free(void *p)
+{
+    if (p && cudaFreeHost(p) != cudaSuccess) cudaGetLastError();
+}
+
+int frb_host_register(void *p, size_t bytes)
+{
+    if (!p || bytes == 0) return fail(FRB_ERR_INVALID, "null or empty buffer");
+    if (frb_device_count() == 0) return fail(FRB_ERR_NO_DEVICE, "no usable CUDA device: pinned memory needs the driver");
+    CU(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+    return FRB_OK;
+}
+
+int frb_host_unregister(void *p)
+{
+    if (!p) return fail(FRB_ERR_INVALID, "null buffer");
+    CU(cudaHostUnregister(p));
+    return FRB_OK;
+}
+
 const char *frb_last_error(void) { return tl_error.c_str(); }
 
 FrbRGB frb_rgb_new(uint8_t r, uint8_t b, uint8_t g)

@@ -138,5 +138,38 @@ inline std::vector<uint8_t> get_image_rgba(const calc::Config &config, int devic
     return image;
 }
 
+// A page-locked RGBA frame for callers that render many frames into the same memory (the GUI's render thread,
+// src/gui.rs:56-82): the GPU writes a pinned destination while it iterates, so nothing is copied after the frame.
+class PinnedFrame {
+public:
+    PinnedFrame() = default;
+    PinnedFrame(const PinnedFrame &) = delete;
+    PinnedFrame &operator=(const PinnedFrame &) = delete;
+    ~PinnedFrame() { frb_host_free(ptr_); }
+    // get_image + the RGB -> RGBA expansion of src/gui.rs:62-75; device -1 = every GPU of the box
+    void render(const calc::Config &config, int device = -1)
+    {
+        const size_t n = (size_t)config.width * config.height * 4;
+        if (n > cap_) {
+            frb_host_free(ptr_);
+            cap_ = n + n / 8 + 4096;
+            ptr_ = static_cast<uint8_t *>(frb_host_alloc(cap_));
+            if (!ptr_) {
+                cap_ = 0;
+                check(FRB_ERR_CUDA, "frb_host_alloc");
+            }
+        }
+        const FrbConfig c = config.to_c();
+        check(frb_render(&c, ptr_, n, FRB_RGBA32, device), "frb_render");
+        len_ = n;
+    }
+    const uint8_t *data() const { return ptr_; }
+    size_t size() const { return len_; }
+
+private:
+    uint8_t *ptr_ = nullptr;
+    size_t cap_ = 0, len_ = 0;
+};
+
 }  // namespace fractal_renderer
 #endif

@@ -238,6 +238,19 @@ int frb_server_poll(FrbServer *server, uint8_t *rgba, size_t len, uint32_t *widt
 int frb_server_stats(FrbServer *server, FrbServerStats *stats);
 const char *frb_server_last_error(FrbServer *server);
 
+/* ---- pinned host memory (optional; lets a binding use the fast output path without linking CUDA itself) ---------- */
+
+/* Page-locked host memory, usable from every device: a destination allocated here is written by the GPU while the
+ * iterations run (frb_render / frb_render_shard) instead of being copied afterwards.  NULL on failure (see
+ * frb_last_error).  Release with frb_host_free.  On the reference side this would back the Vec<RGB> that get_image
+ * returns (src/lib.rs:253) or the GUI's frame (src/gui.rs:62-75) through a custom allocator / Box<[u8]>. */
+void *frb_host_alloc(size_t bytes);
+void frb_host_free(void *p);
+/* Pins caller-owned memory in place (e.g. a long-lived frame buffer) / undoes it.  Pinning costs about a millisecond
+ * per 10 MB: worth it for buffers that are rendered into many times. */
+int frb_host_register(void *p, size_t bytes);
+int frb_host_unregister(void *p);
+
 /* ---- diagnostics ---------------------------------------------------------------------------------------- */
 
 /* Message for the last error on this thread ("" if none). Valid until the next failing call on this thread. */

@@ -49,6 +49,8 @@ extern "C" {
     pub fn frb_render_fern(cfg: *const FrbConfig, threads: u32, seed: u64, shard: *const core::ffi::c_void, out: *mut u8,
                            out_len: usize, format: u32, device: c_int) -> c_int;
     pub fn frb_last_error() -> *const c_char;
+    pub fn frb_host_alloc(bytes: usize) -> *mut core::ffi::c_void;
+    pub fn frb_host_free(p: *mut core::ffi::c_void);
 }
 
 impl From<&Config> for FrbConfig {
@@ -110,4 +112,64 @@ pub fn get_image_fern_b200(config: &Config) -> Vec<RGB> {
     }
     unsafe { image.set_len(n) };
     image
+}
+
+/// A page-locked RGBA frame for callers that render many frames into the same memory — the GUI's render thread
+/// (src/gui.rs:56-82): the GPU writes a pinned destination while it iterates, so nothing is copied after the frame.
+/// `render` replaces `get_image(&config)` + the RGB->RGBA expansion of src/gui.rs:62-75; `as_rgba` is what
+/// `ColorImage::from_rgba_unmultiplied` takes.
+pub struct PinnedFrame {
+    ptr: *mut u8,
+    cap: usize,
+    len: usize,
+}
+
+unsafe impl Send for PinnedFrame {}
+
+impl PinnedFrame {
+    pub fn new() -> Self {
+        PinnedFrame { ptr: core::ptr::null_mut(), cap: 0, len: 0 }
+    }
+    fn reserve(&mut self, bytes: usize) {
+        if bytes <= self.cap {
+            return;
+        }
+        unsafe {
+            if !self.ptr.is_null() {
+                frb_host_free(self.ptr as *mut core::ffi::c_void);
+            }
+            let want = bytes + bytes / 8 + 4096; // head-room: window resizes should not re-pin every frame
+            self.ptr = frb_host_alloc(want) as *mut u8;
+            if self.ptr.is_null() {
+                let msg = CStr::from_ptr(frb_last_error()).to_string_lossy().into_owned();
+                panic!("frb_host_alloc failed: {}", msg);
+            }
+            self.cap = want;
+        }
+    }
+    pub fn render(&mut self, config: &Config) {
+        let n = config.width as usize * config.height as usize * 4;
+        self.reserve(n);
+        let cfg = FrbConfig::from(config);
+        let rc = unsafe { frb_render(&cfg, self.ptr, n, FRB_RGBA32, -1) };
+        if rc != 0 {
+            let msg = unsafe { CStr::from_ptr(frb_last_error()) }.to_string_lossy().into_owned();
+            panic!("frb_render failed ({}): {}", rc, msg);
+        }
+        self.len = n;
+    }
+    pub fn as_rgba(&self) -> &[u8] {
+        if self.len == 0 {
+            return &[];
+        }
+        unsafe { core::slice::from_raw_parts(self.ptr, self.len) }
+    }
+}
+
+impl Drop for PinnedFrame {
+    fn drop(&mut self) {
+        if !self.ptr.is_null() {
+            unsafe { frb_host_free(self.ptr as *mut core::ffi::c_void) };
+        }
+    }
 }

@@ -176,3 +176,27 @@ print("ok")
 '''
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_library_pinned_allocations_take_the_streamed_path(gpu):
+    """frb_host_alloc / frb_host_register (what a binding without CUDA of its own uses) give destinations the finisher streams into."""
+    import ctypes
+    from fractal_renderer_b200 import _lib
+    cfg = configs.c1().with_(width=1280, height=720, iterations=600)
+    ref = render_ordinary(gpu, cfg, 3)
+    buf = gpu.pinned_empty(cfg.width * cfg.height * 3)
+    buf[:] = 0x5A
+    got = gpu.render_shard(cfg, gpu.Shard(), 3, out=buf.reshape(cfg.height, cfg.width, 3))
+    assert gpu.last_stats()["kernel_launches"] == 3 and np.array_equal(got, ref)
+    del got, buf
+    own = np.zeros(cfg.width * cfg.height * 3 + 4096, np.uint8)
+    base = (own.ctypes.data + 4095) & ~4095
+    view = own[base - own.ctypes.data: base - own.ctypes.data + cfg.width * cfg.height * 3]
+    lib = _lib.load()
+    _lib.check(lib.frb_host_register(ctypes.c_void_p(view.ctypes.data), view.nbytes))
+    try:
+        got = gpu.render_shard(cfg, gpu.Shard(), 3, out=view.reshape(cfg.height, cfg.width, 3))
+        assert gpu.last_stats()["kernel_launches"] == 3 and np.array_equal(got, ref)
+    finally:
+        _lib.check(lib.frb_host_unregister(ctypes.c_void_p(view.ctypes.data)))
+    assert lib.frb_host_register(None, 16) == -2
