@@ -85,6 +85,11 @@ def test_no_device_fails_loudly():
         f.init(0)
     with pytest.raises(f.FrbError):
         f.measure_fp64_peak(0)
+    with pytest.raises(f.FrbError) as e:
+        f.pinned_empty(1024)          # pinned memory needs the driver: no quiet malloc in its place
+    import ctypes
+    buf = (ctypes.c_uint8 * 4096)()
+    assert _lib.load().frb_host_register(buf, 4096) == _lib.FRB_ERR_NO_DEVICE
 
 
 def test_product_never_touches_the_oracle():
