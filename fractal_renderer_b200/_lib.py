@@ -62,6 +62,7 @@ EXPORTS = (
     "frb_server_destroy",
     "frb_server_request",
     "frb_server_poll",
+    "frb_server_acquire",
     "frb_server_stats",
     "frb_server_last_error",
 )
@@ -187,6 +188,8 @@ def load() -> ctypes.CDLL:
     L.frb_server_destroy.argtypes = [ctypes.c_void_p]
     L.frb_server_request.restype = ctypes.c_int
     L.frb_server_request.argtypes = [ctypes.c_void_p, P(FrbConfig)]
+    L.frb_server_acquire.restype = ctypes.c_int
+    L.frb_server_acquire.argtypes = [ctypes.c_void_p, P(ctypes.c_void_p), P(ctypes.c_uint32), P(ctypes.c_uint32), ctypes.c_int]
     L.frb_server_poll.restype = ctypes.c_int
     L.frb_server_poll.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, P(ctypes.c_uint32), P(ctypes.c_uint32),
                                   ctypes.c_int]

@@ -87,6 +87,7 @@ struct Server {
     FrbConfig request = {};
     // the shared `image: Arc<Mutex<Option<ColorImage>>>`
     FrameBuf image;
+    FrameBuf held;                     // the frame last handed out by frb_server_acquire (owned by the caller until the next one)
     bool pin_frames = false;           // the library's own renderer: frames in pinned memory
     uint32_t image_w = 0, image_h = 0;
     bool image_fresh = false;
@@ -194,11 +195,10 @@ int frb_server_request(FrbServer *h, const FrbConfig *cfg)
     return FRB_OK;
 }
 
-int frb_server_poll(FrbServer *h, uint8_t *rgba, size_t len, uint32_t *width, uint32_t *height, int timeout_ms)
+// Waits (up to timeout_ms; < 0 = for ever) for a fresh frame or an error.  Caller holds `lk`.  Returns 1 (fresh frame in the
+// slot), 0 (none) or the render error, which it clears.
+static int wait_frame(Server *s, std::unique_lock<std::mutex> &lk, int timeout_ms)
 {
-    Server *s = reinterpret_cast<Server *>(h);
-    if (!s) return FRB_ERR_INVALID;
-    std::unique_lock<std::mutex> lk(s->mu);
     if (timeout_ms != 0 && !s->image_fresh && s->last_rc == FRB_OK) {
         auto ready = [&] { return s->image_fresh || s->last_rc != FRB_OK || (!s->working && !s->have_request); };
         if (timeout_ms < 0)
@@ -211,7 +211,16 @@ int frb_server_poll(FrbServer *h, uint8_t *rgba, size_t len, uint32_t *width, ui
         s->last_rc = FRB_OK;
         return rc;
     }
-    if (!s->image_fresh) return 0;
+    return s->image_fresh ? 1 : 0;
+}
+
+int frb_server_poll(FrbServer *h, uint8_t *rgba, size_t len, uint32_t *width, uint32_t *height, int timeout_ms)
+{
+    Server *s = reinterpret_cast<Server *>(h);
+    if (!s) return FRB_ERR_INVALID;
+    std::unique_lock<std::mutex> lk(s->mu);
+    const int st = wait_frame(s, lk, timeout_ms);
+    if (st <= 0) return st;
     // `app.image.lock().unwrap().take()` (src/gui.rs:110) and the re-request of :115-117
     const size_t bytes = (size_t)s->image_w * s->image_h * 4;
     if (width) *width = s->image_w;
@@ -220,6 +229,23 @@ int frb_server_poll(FrbServer *h, uint8_t *rgba, size_t len, uint32_t *width, ui
     if (len < bytes) return FRB_ERR_INVALID;
     memcpy(rgba, s->image.p, bytes);
     s->image_fresh = false;
+    if (s->try_redraw) request_locked(s);
+    return 1;
+}
+
+int frb_server_acquire(FrbServer *h, const uint8_t **rgba, uint32_t *width, uint32_t *height, int timeout_ms)
+{
+    Server *s = reinterpret_cast<Server *>(h);
+    if (!s || !rgba) return FRB_ERR_INVALID;
+    std::unique_lock<std::mutex> lk(s->mu);
+    const int st = wait_frame(s, lk, timeout_ms);
+    if (st <= 0) return st;
+    // the frame moves out of the slot; the buffer handed out last time goes back into circulation
+    s->held.swap(s->image);
+    s->image_fresh = false;
+    *rgba = s->held.p;
+    if (width) *width = s->image_w;
+    if (height) *height = s->image_h;
     if (s->try_redraw) request_locked(s);
     return 1;
 }

@@ -108,8 +108,20 @@ class FrameServer:
         c = config.to_c()
         _lib.check(self._lib.frb_server_request(self._h, ctypes.byref(c)))
 
-    def poll(self, timeout_ms: int = 0) -> Optional[np.ndarray]:
+    def poll(self, timeout_ms: int = 0, copy: bool = True) -> Optional[np.ndarray]:
+        """The newest finished frame as (H, W, 4) uint8, or None.  copy=False hands out the server's own (pinned) frame without
+        copying it (frb_server_acquire): the array is only valid until the next poll that returns a frame, or close()."""
         w, h = ctypes.c_uint32(), ctypes.c_uint32()
+        if not copy:
+            ptr = ctypes.c_void_p()
+            rc = self._lib.frb_server_acquire(self._h, ctypes.byref(ptr), ctypes.byref(w), ctypes.byref(h), timeout_ms)
+            if rc < 0:
+                raise _lib.FrbError(rc, self._lib.frb_server_last_error(self._h).decode("utf-8", "replace"))
+            if rc == 0:
+                return None
+            n = h.value * w.value * 4
+            raw = (ctypes.c_uint8 * max(n, 1)).from_address(ptr.value)
+            return np.frombuffer(raw, dtype=np.uint8, count=n).reshape(h.value, w.value, 4)
         for _ in range(8):
             # peek (waits, reports the size), then take; a newer frame of another size may slip in between: retry
             rc = self._lib.frb_server_poll(self._h, None, 0, ctypes.byref(w), ctypes.byref(h), timeout_ms)

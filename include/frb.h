@@ -235,6 +235,11 @@ int frb_server_request(FrbServer *server, const FrbConfig *cfg);
  * failed (or `len` is too small).  rgba == NULL peeks: reports the size and leaves the frame in the slot.
  * timeout_ms: 0 = do not wait, < 0 = wait for a frame. */
 int frb_server_poll(FrbServer *server, uint8_t *rgba, size_t len, uint32_t *width, uint32_t *height, int timeout_ms);
+/* Like frb_server_poll, without the copy: hands out the finished frame itself — `*rgba` points at width*height*4 bytes
+ * of the server's (pinned) memory and stays valid until the next frb_server_acquire / frb_server_poll that returns a
+ * frame, or frb_server_destroy.  This is the reference's `image.lock().unwrap().take()` (src/gui.rs:110): ownership of
+ * the frame moves to the UI side; the render thread keeps working in its other two buffers.  Returns 1 / 0 / <0 as poll. */
+int frb_server_acquire(FrbServer *server, const uint8_t **rgba, uint32_t *width, uint32_t *height, int timeout_ms);
 int frb_server_stats(FrbServer *server, FrbServerStats *stats);
 const char *frb_server_last_error(FrbServer *server);
 

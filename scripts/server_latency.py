@@ -23,13 +23,14 @@ with FrameServer(device=0) as srv:
         for _ in range(3):
             srv.request(view.config); srv.poll(10000)
         n = 50
-        lat = []
-        for k in range(n):
-            view.apply_scroll(1.0 if k % 2 else -1.0)   # a zoom step each frame, like a scroll-wheel drag
-            t = time.perf_counter()
-            srv.request(view.config)
-            frame = srv.poll(10000)
-            lat.append(time.perf_counter() - t)
-            assert frame is not None
-        lat = np.array(lat) * 1e3
-        print(f"{name}: median {np.median(lat):.3f} ms  p95 {np.percentile(lat, 95):.3f} ms  -> {1e3 / np.median(lat):.0f} frames/s", flush=True)
+        for copy in (True, False):   # frb_server_poll into a fresh array / frb_server_acquire (the frame itself)
+            lat = []
+            for k in range(n):
+                view.apply_scroll(1.0 if k % 2 else -1.0)   # a zoom step each frame, like a scroll-wheel drag
+                t = time.perf_counter()
+                srv.request(view.config)
+                frame = srv.poll(10000, copy=copy)
+                lat.append(time.perf_counter() - t)
+                assert frame is not None
+            lat = np.array(lat) * 1e3
+            print(f"{name} [{'poll' if copy else 'acquire'}]: median {np.median(lat):.3f} ms  p95 {np.percentile(lat, 95):.3f} ms  -> {1e3 / np.median(lat):.0f} frames/s", flush=True)

@@ -115,3 +115,28 @@ def test_frame_server_frames_are_streamed_into_pinned_memory(gpu):
             frame = srv.poll(10000)
             assert frame is not None and frame.shape[:2] == (cfg.height, cfg.width)
             assert np.array_equal(frame, gpu.get_image_rgba(cfg)), (cfg.width, cfg.height)
+
+
+def test_frame_server_acquire_hands_out_frames_without_copying():
+    """frb_server_acquire: the frame itself moves to the caller (src/gui.rs:110 `take()`), three buffers rotate, and a frame
+    stays intact while the next ones are rendered and taken by copy."""
+    def renderer(cfg):
+        return np.full((cfg.height, cfg.width, 4), cfg.iterations % 256, np.uint8)
+
+    base = Config.new(Algo.Mandelbrot).with_(width=32, height=8)
+    with FrameServer(renderer=renderer) as srv:
+        assert srv.poll(0, copy=False) is None
+        srv.request(base.with_(iterations=7))
+        a = srv.poll(2000, copy=False)
+        assert a is not None and a.shape == (8, 32, 4) and (a == 7).all()
+        srv.request(base.with_(iterations=9, width=16))
+        b = srv.poll(2000)                      # by copy: does not disturb the acquired frame
+        assert (b == 9).all() and b.shape == (8, 16, 4) and (a == 7).all()
+        srv.request(base.with_(iterations=11))
+        c = srv.poll(2000, copy=False)          # a's buffer goes back into circulation now
+        assert (c == 11).all() and c.shape == (8, 32, 4)
+        for it in range(20, 30):                # keep rotating: every frame is the one requested
+            srv.request(base.with_(iterations=it))
+            f = srv.poll(2000, copy=False)
+            assert f is not None and (f == it).all()
+        assert srv.stats()["frames_rendered"] == 13
