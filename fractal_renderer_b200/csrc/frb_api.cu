@@ -1547,6 +1547,8 @@ int frb_render_frames(const FrbConfig *cfgs, uint32_t n, uint8_t *out, size_t ou
         devs.push_back(device);
     else
         devs = active_devices();
+    // every context is locked once for the whole call: a device listed twice (FRB_TUNE_FAKE_DEVICES) counts once
+    devs.erase(std::unique(devs.begin(), devs.end()), devs.end());
     if (devs.empty()) return fail(FRB_ERR_NO_DEVICE, "no usable CUDA device; this library has no CPU path");
     const double t0 = now_ms();
     // Frames are independent; frame k -> device k % G (round robin balances the 80x cost spread of a zoom to
