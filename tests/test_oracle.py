@@ -85,7 +85,8 @@ def test_golden_vectors_frozen():
 @pytest.mark.parametrize("name", ["mandel_default", "mandel_iter0", "mandel_iter1", "mandel_no_smooth", "mandel_no_inside",
                                   "mandel_aniso_scale", "mandel_tall", "mandel_limit1p5", "mandel_limit1e155",
                                   "mandel_colors_255", "mandel_exposure_neg", "julia_default", "julia_zero", "fern_black",
-                                  "mandel_deep_subulp", "mandel_stable_big"])
+                                  "mandel_deep_subulp", "mandel_stable_big", "mandel_iter15", "mandel_iter50", "mandel_iter300",
+                                  "julia_iter301", "mandel_c2_view", "julia_c3_view"])
 def test_oracle_vs_independent_python_restatement(name):
     """tests/pyref.py restates the spec with Python floats (IEEE binary64, no fusion); same bits."""
     cfg = cases.all_small_cases()[name]
