@@ -117,6 +117,13 @@ frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
     uint32_t next_chunk = 0;
     if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
     uint32_t trips = 0;  // warp-uniform
+#ifdef FRB_STREAM_TRACE
+    if (lane == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        atomicMin(p.stats + 13, t);
+    }
+#endif
     // Watermark for the streaming finisher (frb_stream.cuh): the lowest pixel index this warp still owes a record for.
     // Published (release) whenever the warp fetched a chunk or the queue is drained, and as 0xffffffff on exit.  A stale
     // value is always a lower bound: the queue hands out increasing chunk ids, so whatever the warp takes next lies above
@@ -157,6 +164,13 @@ frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
                             const uint32_t c = __shfl_sync(FULL, next_chunk, 0);
                             if (c >= p.total_chunks) {
                                 drained = true;
+#ifdef FRB_STREAM_TRACE
+                                if (lane == 0) {
+                                    unsigned long long t;
+                                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                                    atomicMin(p.stats + 9, t);
+                                }
+#endif
                                 break;
                             }
                             if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
@@ -223,6 +237,8 @@ frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
         __threadfence();
         __syncwarp();
         if (lane == 0) *reinterpret_cast<volatile uint32_t *>(wm) = 0xffffffffu;
+    }
+    {
 #ifdef FRB_STREAM_TRACE
         if (lane == 0) {
             unsigned long long t;

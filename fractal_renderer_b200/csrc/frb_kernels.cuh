@@ -130,6 +130,7 @@ __global__ void frb_coord_tables_kernel(const __grid_constant__ RenderParams p)
         }
 #ifdef FRB_STREAM_TRACE
         p.stats[3] = ~0ull; p.stats[4] = ~0ull; p.stats[5] = 0ull; p.stats[6] = 0ull; p.stats[7] = ~0ull;
+        p.stats[9] = ~0ull; p.stats[13] = ~0ull;  // queue drained (first warp to see it), first iterate warp running
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(p.stats[8]));
 #endif
     }
