@@ -22,7 +22,7 @@ from typing import Optional, Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import (FRB_RGB24, FRB_RGBA32, KERNEL_AUTO, KERNEL_DEFER6, KERNEL_DENSE6, KERNEL_TILE, KERNEL_NAMES, KERNEL_SIMPLE, KERNEL_STREAM6, KERNEL_STREAM7,
+from ._lib import (FRB_RGB24, FRB_RGBA32, KERNEL_AUTO, KERNEL_DEFER6, KERNEL_DENSE6, KERNEL_TILE, KERNEL_NAMES, KERNEL_SIMPLE, KERNEL_STREAM7,
                    FrbError, FrbFp64Peak, FrbShard, FrbStats)
 from .calc import RGB, Algo, Config, FrbConfig, Imaginary
 
@@ -30,7 +30,8 @@ __all__ = [
     "Algo", "Config", "Imaginary", "RGB", "FrbError", "Shard", "get_image", "get_image_rgba", "get_image_into",
     "render_shard", "render_counts", "render_frames", "render_device_async", "sync_stats", "async_stats", "last_stats",
     "device_count", "init", "shutdown", "render_fern", "fern_default_threads", "set_kernel_variant", "measure_fp64_peak", "shard_rows", "shard_row_to_y",
-    "FRB_RGB24", "FRB_RGBA32", "pinned_empty", "KERNEL_AUTO", "KERNEL_STREAM6", "KERNEL_STREAM7", "KERNEL_SIMPLE", "KERNEL_DENSE6", "KERNEL_DEFER6", "KERNEL_TILE", "KERNEL_NAMES",
+    "init_list", "set_tuning", "render_bands", "SharedFrame",
+    "FRB_RGB24", "FRB_RGBA32", "pinned_empty", "KERNEL_AUTO", "KERNEL_STREAM7", "KERNEL_SIMPLE", "KERNEL_DENSE6", "KERNEL_DEFER6", "KERNEL_TILE", "KERNEL_NAMES",
 ]
 
 
@@ -70,6 +71,17 @@ def init(device_mask: int = 0) -> None:
     _lib.check(_lib.load().frb_init(device_mask))
 
 
+def init_list(devices: Sequence[int]) -> None:
+    """Explicit device list for device = -1 renders: shard i of len(devices) goes to devices[i]; a device may repeat."""
+    arr = (ctypes.c_int32 * len(devices))(*devices)
+    _lib.check(_lib.load().frb_init_list(arr, len(devices)))
+
+
+def set_tuning(name: str, value: int) -> None:
+    """Tuning build only (FRB_LIB_PATH=.../libfrb_tune.so): the product library rejects every knob."""
+    _lib.check(_lib.load().frb_set_tuning(name.encode(), int(value)))
+
+
 def shutdown() -> None:
     _lib.load().frb_shutdown()
 
@@ -100,6 +112,11 @@ def get_image_into(config: Config, out: np.ndarray, fmt: int = FRB_RGB24, device
     if out.dtype != np.uint8 or not out.flags.c_contiguous:
         raise ValueError("out must be a C-contiguous uint8 array")
     c = config.to_c()
+    if config.algo == Algo.BarnsleyFern:
+        # get_image's other arm (src/lib.rs:271-319): rayon's thread count, fresh entropy — as the reference
+        seed = int.from_bytes(os.urandom(8), "little")
+        _lib.check(_lib.load().frb_render_fern(ctypes.byref(c), 0, seed, None, out.ctypes.data, out.nbytes, fmt, max(device, 0)))
+        return out
     _lib.check(_lib.load().frb_render(ctypes.byref(c), out.ctypes.data, out.nbytes, fmt, device))
     return out
 
@@ -122,8 +139,6 @@ def get_image(config: Config, device: int = 0) -> np.ndarray:
     """`get_image(&Config) -> Vec<RGB>` (src/lib.rs:253): (H*W, 3) uint8, row-major, fields r,g,b.  Like the reference it
     dispatches on the algorithm: Mandelbrot | Julia -> the per-pixel path, BarnsleyFern -> the chaos game with rayon's
     thread count and a fresh entropy seed (src/lib.rs:271-319, 428)."""
-    if config.algo == Algo.BarnsleyFern:
-        return render_fern(config, device=max(device, 0)).reshape(-1, 3)
     out = np.empty((config.height * config.width, 3), np.uint8)
     return get_image_into(config, out, FRB_RGB24, device)
 
@@ -164,6 +179,46 @@ def render_shard(config: Config, shard: Shard, fmt: int = FRB_RGB24, device: int
     s, p = _shard_ptr(shard)
     _lib.check(_lib.load().frb_render_shard(ctypes.byref(c), p, out.ctypes.data, out.nbytes, fmt, device))
     return out
+
+
+def render_bands(config: Config, shard: Shard, frame: np.ndarray, fmt: int = FRB_RGB24, device: int = 0) -> np.ndarray:
+    """One shard of the frame written into ITS PLACE in the whole image `frame` (>= H*W*fmt bytes, shared by all shards)."""
+    if frame.dtype != np.uint8 or not frame.flags.c_contiguous:
+        raise ValueError("frame must be a C-contiguous uint8 array")
+    c = config.to_c()
+    s, p = _shard_ptr(shard)
+    _lib.check(_lib.load().frb_render_bands(ctypes.byref(c), p, frame.ctypes.data, frame.nbytes, fmt, device))
+    return frame
+
+
+class SharedFrame:
+    """One host image for a one-process-per-GPU job (frb_shared_frame_*): POSIX shared memory mapped — and, with a GPU, pinned —
+    by every rank, so that each rank's render_bands lands in the same frame; `barrier()` = the whole frame is on the host."""
+
+    def __init__(self, name: str, nbytes: int, ranks: int, rank: int):
+        self._lib = _lib.load()
+        self._h = self._lib.frb_shared_frame_open(name.encode(), int(nbytes), ranks, rank)
+        if not self._h:
+            raise _lib.FrbError(_lib.FRB_ERR_INVALID, self._lib.frb_last_error().decode("utf-8", "replace"))
+        ptr = self._lib.frb_shared_frame_data(self._h)
+        raw = (ctypes.c_uint8 * max(int(nbytes), 1)).from_address(ptr)
+        self.array = np.frombuffer(raw, dtype=np.uint8, count=int(nbytes))
+        self.pinned = bool(self._lib.frb_shared_frame_pinned(self._h))
+
+    def barrier(self) -> None:
+        _lib.check(self._lib.frb_shared_frame_barrier(self._h))
+
+    def close(self) -> None:
+        if self._h:
+            self.array = None
+            self._lib.frb_shared_frame_close(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
 
 
 def render_counts(config: Config, shard: Optional[Shard] = None, device: int = 0, want_z: bool = True):

@@ -11,7 +11,8 @@ import os
 from .calc import FrbConfig
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.environ.get("FRB_LIB_PATH") or os.path.join(_HERE, "libfrb.so")  # FRB_LIB_PATH: instrumented debug builds
+LIB_PATH = os.environ.get("FRB_LIB_PATH") or os.path.join(_HERE, "libfrb.so")  # FRB_LIB_PATH: the tuning / trace builds
+TUNE_LIB_PATH = os.path.join(_HERE, "libfrb_tune.so")  # -DFRB_TUNING build: frb_set_tuning works (sweeps, two tests)
 
 FRB_RGB24 = 3
 FRB_RGBA32 = 4
@@ -23,13 +24,12 @@ FRB_ERR_CUDA = -3
 FRB_ERR_TOO_LARGE = -4
 
 KERNEL_AUTO = 0
-KERNEL_STREAM6 = 1
 KERNEL_STREAM7 = 2
 KERNEL_SIMPLE = 3
 KERNEL_DENSE6 = 4
 KERNEL_DEFER6 = 5
 KERNEL_TILE = 6
-KERNEL_NAMES = {0: "auto", 1: "stream6", 2: "stream7", 3: "simple", 4: "dense6", 5: "defer6", 6: "tile"}
+KERNEL_NAMES = {0: "auto", 2: "stream7", 3: "simple", 4: "dense6", 5: "defer6", 6: "tile"}
 
 # every symbol include/frb.h declares; tests/test_abi.py checks the library exports exactly these
 EXPORTS = (
@@ -40,10 +40,13 @@ EXPORTS = (
     "frb_shard_row_to_y",
     "frb_device_count",
     "frb_init",
+    "frb_init_list",
     "frb_shutdown",
     "frb_set_kernel_variant",
+    "frb_set_tuning",
     "frb_render",
     "frb_render_shard",
+    "frb_render_bands",
     "frb_render_counts",
     "frb_render_frames",
     "frb_render_fern",
@@ -65,6 +68,11 @@ EXPORTS = (
     "frb_server_acquire",
     "frb_server_stats",
     "frb_server_last_error",
+    "frb_shared_frame_open",
+    "frb_shared_frame_data",
+    "frb_shared_frame_pinned",
+    "frb_shared_frame_barrier",
+    "frb_shared_frame_close",
 )
 
 
@@ -149,6 +157,22 @@ def load() -> ctypes.CDLL:
     L.frb_device_count.argtypes = []
     L.frb_init.restype = ctypes.c_int
     L.frb_init.argtypes = [ctypes.c_uint32]
+    L.frb_init_list.restype = ctypes.c_int
+    L.frb_init_list.argtypes = [P(ctypes.c_int32), ctypes.c_uint32]
+    L.frb_set_tuning.restype = ctypes.c_int
+    L.frb_set_tuning.argtypes = [ctypes.c_char_p, ctypes.c_int64]
+    L.frb_render_bands.restype = ctypes.c_int
+    L.frb_render_bands.argtypes = [P(FrbConfig), P(FrbShard), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_int]
+    L.frb_shared_frame_open.restype = ctypes.c_void_p
+    L.frb_shared_frame_open.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_uint32]
+    L.frb_shared_frame_data.restype = ctypes.c_void_p
+    L.frb_shared_frame_data.argtypes = [ctypes.c_void_p]
+    L.frb_shared_frame_pinned.restype = ctypes.c_int
+    L.frb_shared_frame_pinned.argtypes = [ctypes.c_void_p]
+    L.frb_shared_frame_barrier.restype = ctypes.c_int
+    L.frb_shared_frame_barrier.argtypes = [ctypes.c_void_p]
+    L.frb_shared_frame_close.restype = None
+    L.frb_shared_frame_close.argtypes = [ctypes.c_void_p]
     L.frb_shutdown.restype = None
     L.frb_shutdown.argtypes = []
     L.frb_set_kernel_variant.restype = ctypes.c_int

@@ -140,15 +140,19 @@ class Config:
 
     @staticmethod
     def cli(algo: Algo = Algo.Mandelbrot, **kw) -> "Config":
-        """The configuration the reference CLI builds with no flags (src/lib.rs:31-234): 750x500, 50 iterations,
-        exposure 5, pos.re -0.6 for Mandelbrot / 0 for Julia — these differ from Config::new."""
+        """The configuration the reference CLI builds with no flags (src/lib.rs:31-234): 750x500, exposure 5, pos.re 0 for
+        julia and -0.6 otherwise (`default_value_if("algo", Some("julia"), Some("0"))`, src/lib.rs:66-71); iterations and both
+        colours come from Config::new(algo) (src/lib.rs:209-222) — so the fern keeps its 10 M points and green-on-grey."""
+        ref = Config.new(algo)
         base = dict(
             algo=algo,
             width=750,
             height=500,
-            iterations=50,
+            iterations=ref.iterations,
             exposure=5.0,
-            pos=Imaginary(-0.6 if algo == Algo.Mandelbrot else 0.0, 0.0),
+            pos=Imaginary(0.0 if algo == Algo.Julia else -0.6, 0.0),
+            primary_color=ref.primary_color,
+            secondary_color=ref.secondary_color,
         )
         base.update(kw)
         return Config(**base)

@@ -33,8 +33,40 @@ constexpr int kMaxDevices = 32;
 constexpr int kSlots = 64;               // in-flight async renders per device whose statistics stay readable
 constexpr uint32_t kDefaultChunk = 64;   // pixels per queue chunk
 constexpr uint32_t kDefaultBandRows = 16;
-constexpr uint32_t kTileMaxIterations = 384;  // iteration caps up to this take the lock-step tile kernel (frb_tile.cuh)
+constexpr uint32_t kMinDeferIterations = 32;  // the deferred kernel needs a few blocks of iterations to be worth its resolve pass
+constexpr uint32_t kMaxDeferIterations = 1u << 30;  // its budget counter shares a word with the escape filter (frb_deferred.cuh)
 constexpr uint32_t kMaxIterWarps = 16384;  // upper bound on resident warps of one iterate launch (SMs x CTAs/SM x 8)
+
+// ---- tuning -----------------------------------------------------------------------------------------------------------------
+// Every choice the library makes per frame (block shape of the deferred kernel, chunk size, slab counts, which host path) has
+// its default here.  A product build (no -DFRB_TUNING) reads nothing else: no environment variable, no hidden switch, the
+// defaults are compile-time constants.  The tuning build (`make tune` -> libfrb_tune.so, used by the sweeps under scripts/ and by
+// two tests that force rarely taken paths) makes them settable through frb_set_tuning().
+struct Tuning {
+    int defer_b = 0;            // deferred kernel: iterations per block (0 = by iteration cap)
+    int defer_nb = 0;           //                  blocks per trip      (0 = by iteration cap)
+    int defer_shape = -1;       //                  index into kDeferShapes (-1 = default)
+    int chunk = 0;              // pixels per queue chunk (0 = by iteration cap)
+    int fast_shade = 1;         // 0 = colour through libdevice log2 and the division sequence
+    int tile_max = 384;         // iteration caps up to this take the lock-step tile kernel
+    int stream = 1;             // 0 = never use the streaming finisher
+    int stream_gen_polls = 20000;  // finisher: bound on the wait for the frame to start (~1 us per poll); 0 forces the fallback
+    int stream_rows = 0;        // finisher: rows per slab (0 = ~256 Kpx)
+    int stream_ctas = 1;        // finisher CTAs per SM
+    int slabs = 0;              // sliced host path: number of row slabs (0 = by frame size)
+    int no_slab = 0;            // 1 = never slice
+    int stage = 1;              // 0 = pageable destinations take the sliced copy path instead of the pinned staging pipeline
+    int copy_threads = 0;       // staging pipeline: host copy threads (0 = default)
+    int end_chunk = 0;          // deferred kernel: pixels per chunk in the end phase of the queue (0 = default)
+    int pool = 1;               // deferred kernel: 0 = no orbit pool (drained warps keep their lanes to the end)
+};
+#ifdef FRB_TUNING
+Tuning g_tuning;
+inline const Tuning &tuning() { return g_tuning; }
+#else
+constexpr Tuning kTuning = {};
+inline const Tuning &tuning() { return kTuning; }
+#endif
 
 thread_local std::string tl_error;
 thread_local int tl_code = 0;
@@ -75,6 +107,7 @@ struct Slot {
     uint32_t launches = 0;
     uint32_t variant = 0;
     bool shaded = false;
+    bool stream_fallback = false;  // the streamed frame was re-shaded by the ordinary kernel (finisher never started or gave up)
     uint64_t tile_key = 0;  // non-zero: the tile kernel was the library's choice for this frame (see tile_key_of)
 };
 
@@ -82,7 +115,7 @@ struct DeviceCtx {
     int dev = -1;
     bool ready = false;
     int sm_count = 0;
-    int iter_blocks_per_sm[3] = {0, 0, 0};  // dense FORM 6, dense FORM 7, sparse FORM 6 (deferred: its MINB template argument)
+    int iter_blocks_per_sm[2] = {0, 0};  // resident CTAs per SM of the dense kernels: FORM 6, FORM 7
     cudaStream_t stream = nullptr;       // the library's own stream for this device
     // tile-kernel feedback: the scene (tile_key_of) whose last tile-kernel frame ran with poor lane utilisation, and for how
     // many more frames the library keeps the lane-refill kernel for it before trying the tile kernel again
@@ -128,6 +161,7 @@ std::mutex g_mu;
 DeviceCtx *g_ctx[kMaxDevices] = {};
 int g_device_count = -1;
 uint32_t g_device_mask = 0;  // devices chosen by frb_init (0 = not initialised)
+std::vector<int> g_device_list;  // frb_init_list: the shards of a device = -1 render go to these, in this order (may repeat)
 
 int device_count_locked()
 {
@@ -178,9 +212,7 @@ int ctx_init(DeviceCtx *c, int dev)
                                                      frb::kIterateThreads, 0));
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->iter_blocks_per_sm[1], frb::frb_iterate_stream_kernel<7>,
                                                      frb::kIterateThreads, 0));
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->iter_blocks_per_sm[2], frb::frb_iterate_sparse_kernel<false, 8>,
-                                                     frb::kIterateThreads, 0));
-    if (c->iter_blocks_per_sm[0] < 1 || c->iter_blocks_per_sm[1] < 1 || c->iter_blocks_per_sm[2] < 1)
+    if (c->iter_blocks_per_sm[0] < 1 || c->iter_blocks_per_sm[1] < 1)
         return fail(FRB_ERR_CUDA, "iterate kernel does not fit on device %d", dev);
     c->ready = true;
     return FRB_OK;
@@ -352,15 +384,19 @@ bool form6_is_exact(const FrbConfig &cfg)
     return true;
 }
 
-// The sparse-check kernel tests for escape once per block of kSparseU iterations; that is only sound when an
-// escaped orbit provably keeps growing (see frb_kernels.cuh): R = |limit| >= 8 and |c| <= R^2/2 - 3R for every pixel.
-bool sparse_is_safe(const FrbConfig &cfg)
+// The deferred kernel tests for escape once per block of B iterations and its resolve pass re-runs at most B + 1 steps after a
+// stop by the filter.  Both are only sound when an orbit that fired the filter provably escapes at once and keeps growing
+// (frb_deferred.cuh): the filter compares high words, i.e. fires for max(re^2, im^2) >= (S/2)(1 - 2^-20), so the next step has
+// |z| >= (R^2/2)(1 - 2^-20) - |c|, and that must exceed R with room to spare: R = |limit| in [8, 2^20] and |c| <= R^2/2 - 3R for
+// every pixel give |z| >= 3R - R^2 2^-21 >= 2.5 R.  (Above R ~ 4.7e6 the truncation slack R^2 2^-21 eats the margin: a near-miss
+// stop need not escape within the resolve bound.  Larger limits take the dense kernel, which tests every iteration.)
+bool deferred_is_safe(const FrbConfig &cfg)
 {
     if (!form6_is_exact(cfg)) return false;
-    if (cfg.iterations < 4u * (uint32_t)frb::kSparseU) return false;  // too short to amortise a block
-    if (cfg.iterations >= frb::kIdleBit) return false;                // the kernel encodes "idle lane" in the counter's top bits
+    if (cfg.iterations < kMinDeferIterations) return false;  // too short to amortise a block
+    if (cfg.iterations >= kMaxDeferIterations) return false;
     const double R = std::fabs(cfg.limit);
-    if (!(R >= 8.0) || !(R <= 1e150)) return false;
+    if (!(R >= 8.0) || !(R <= 1048576.0)) return false;
     double cmax;
     if (cfg.algo == FRB_ALGO_JULIA) {
         cmax = std::hypot(cfg.julia_set.re, cfg.julia_set.im);
@@ -375,13 +411,14 @@ bool sparse_is_safe(const FrbConfig &cfg)
     return cmax * 1.0000001 <= 0.5 * R * R - 3.0 * R;
 }
 
-// CTA shapes of the deferred kernel: threads per CTA x resident CTAs per SM (FRB_TUNE_SHAPE picks by index).  Co-resident
+// CTA shapes of the deferred kernel: threads per CTA x resident CTAs per SM (the tuning build can pick any by index).  Co-resident
 // CTAs are served very unevenly by the warp scheduler (frb_deferred.cuh), hence one wide CTA per SM by default.
 struct DeferShape {
     int threads, per_sm;
 };
 constexpr DeferShape kDeferShapes[] = {{256, 3}, {512, 1}, {768, 1}, {1024, 1}, {512, 2}, {256, 2}};
 constexpr int kDeferShapeCount = (int)(sizeof(kDeferShapes) / sizeof(kDeferShapes[0]));
+constexpr int kDeferDefaultShape = 2;
 
 // Shape of the deferred kernel (FRB_KERNEL_DEFER6): B iterations per block, NB blocks per trip, CTA shape.
 // Lanes that stop idle until the trip ends and a stopped pixel costs ~B/2 wasted + ~B/2 resolved iterations, so short
@@ -390,21 +427,23 @@ void choose_deferred_shape(const FrbConfig &cfg, int *b, int *nb, int *minb)
 {
     *b = cfg.iterations >= 2048u ? 16 : 8;
     *nb = cfg.iterations >= 2048u ? 4 : (cfg.iterations >= 256u ? 4 : 1);
-    *minb = 2;  // index into kDeferShapes
-    if (const char *e = getenv("FRB_TUNE_DB")) *b = atoi(e);      // tuning hooks (bench sweeps)
-    if (const char *e = getenv("FRB_TUNE_NB")) *nb = atoi(e);
-    if (const char *e = getenv("FRB_TUNE_SHAPE")) *minb = atoi(e);
+    *minb = kDeferDefaultShape;
+    const Tuning &t = tuning();
+    if (t.defer_b) *b = t.defer_b;
+    if (t.defer_nb) *nb = t.defer_nb;
+    if (t.defer_shape >= 0) *minb = t.defer_shape;
     if (*b != 8 && *b != 16 && *b != 32) *b = 16;
     if (*nb != 1 && *nb != 2 && *nb != 4 && *nb != 8) *nb = 4;
     if (*b == 32 && *nb == 8) *nb = 4;
     if (*b == 32 && *nb == 1) *nb = 2;
     if (*b == 16 && *nb == 1) *nb = 2;
-    if (*minb < 0 || *minb >= kDeferShapeCount) *minb = 2;
+    if (*minb < 0 || *minb >= kDeferShapeCount) *minb = kDeferDefaultShape;
 }
 
 struct Plan {
     RenderParams p;
     uint32_t variant;
+    bool fern;      // algo = BarnsleyFern: the per-pixel path is all black (calc/src/lib.rs:211); no iterate kernel runs
     int tile_form;  // tile kernel: 6- or 7-instruction iteration
     uint64_t tile_key;  // non-zero when AUTO chose the tile kernel
     int defer_b, defer_nb, defer_minb;  // deferred kernel: iterations per block, blocks per trip, CTA shape (index into kDeferShapes)
@@ -456,7 +495,7 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     // 32-pixel segments balance the end of a long-iteration frame better (C2: 5.00 vs 5.09 ms); short-iteration frames
     // (C1, C3) prefer fewer queue transactions (measured, profiles/r1_tuning_sweeps.txt)
     p.chunk = cfg.iterations >= 2048u ? 32u : kDefaultChunk;
-    if (const char *e = getenv("FRB_TUNE_CHUNK")) p.chunk = std::max(1, atoi(e));  // tuning hook (bench sweeps)
+    if (tuning().chunk > 0) p.chunk = (uint32_t)tuning().chunk;
     p.chunks_per_row = cfg.width ? (cfg.width + p.chunk - 1) / p.chunk : 0;
     const uint64_t npix = (uint64_t)p.rows * cfg.width;
     const uint64_t chunks = (uint64_t)p.rows * p.chunks_per_row;
@@ -476,27 +515,28 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     p.primary = (uint32_t)cfg.primary_color.r | ((uint32_t)cfg.primary_color.g << 8) | ((uint32_t)cfg.primary_color.b << 16);
     p.secondary = (uint32_t)cfg.secondary_color.r | ((uint32_t)cfg.secondary_color.g << 8) | ((uint32_t)cfg.secondary_color.b << 16);
     p.format = format;
-    // colour fast path (shade_pixel): uniform conversions done once here; FRB_TUNE_FASTSHADE=0 keeps libdevice's log2 and the
-    // division sequence (the parity tests compare the two)
+    // colour fast path (shade_pixel): uniform conversions done once here (the tuning build can switch it off: a test compares
+    // it with libdevice's log2 and the division sequence)
     p.iterations_d = (double)cfg.iterations;
     p.inv_iterations = cfg.iterations ? 1.0 / p.iterations_d : 0.0;
     p.prim_r = (double)cfg.primary_color.r;
     p.prim_g = (double)cfg.primary_color.g;
     p.prim_b = (double)cfg.primary_color.b;
     p.fast_shade = (cfg.iterations >= 1u && std::isfinite(cfg.exposure) && std::fabs(cfg.exposure) < 1e290) ? 1u : 0u;
-    if (const char *e = getenv("FRB_TUNE_FASTSHADE")) p.fast_shade = (p.fast_shade && atoi(e) != 0) ? 1u : 0u;
+    if (!tuning().fast_shade) p.fast_shade = 0u;
     plan->npix = npix;
     plan->out_bytes = (size_t)npix * format;
     uint32_t v = tl_variant;
     // A forced variant is a request: outside its proven domain it is downgraded to the next kernel that is exact
-    // (STREAM6 -> DENSE6 -> STREAM7); FrbStats.kernel_variant reports what actually ran.
+    // (DEFER6 -> DENSE6 -> STREAM7); FrbStats.kernel_variant reports what actually ran.
     // short orbits, image wanted: the lock-step tile kernel (per-pixel costs of the refill kernels outweigh their lane
-    // utilisation there; FRB_TUNE_TILEMAX moves the threshold).  It has no raw-result output: format 0 falls through.
-    uint32_t tile_max = kTileMaxIterations;
-    if (const char *e = getenv("FRB_TUNE_TILEMAX")) tile_max = (uint32_t)std::max(0, atoi(e));
-    if (v == FRB_KERNEL_TILE && (format == 0 || cfg.algo == FRB_ALGO_BARNSLEY_FERN)) v = FRB_KERNEL_AUTO;
+    // utilisation there).  It has no raw-result output (format 0 falls through), and its grid puts 8 rows on blockIdx.y.
+    const uint32_t tile_max = (uint32_t)std::max(0, tuning().tile_max);
+    const bool tile_fits = (p.rows + 7u) / 8u <= 65535u;
+    plan->fern = cfg.algo == FRB_ALGO_BARNSLEY_FERN;  // get_recursive_pixel returns BLACK for it: nothing to iterate
+    if (v == FRB_KERNEL_TILE && (format == 0 || plan->fern || !tile_fits)) v = FRB_KERNEL_AUTO;
     plan->tile_key = 0;
-    if (v == FRB_KERNEL_AUTO && format != 0 && cfg.iterations <= tile_max && cfg.algo != FRB_ALGO_BARNSLEY_FERN) {
+    if (v == FRB_KERNEL_AUTO && format != 0 && cfg.iterations <= tile_max && !plan->fern && tile_fits) {
         // The cap says nothing about how orbit lengths are mixed inside a tile, and lock-step warps pay for the longest lane
         // (C3-like Julia dust: utilisation 0.38, 2.5x slower than the refill kernel).  The kernel reports its utilisation, so a
         // scene that did badly stays with the refill kernel for the next kTileBackoffFrames frames (harvest()).
@@ -509,8 +549,7 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
         }
     }
     plan->tile_form = form6_is_exact(cfg) ? 6 : 7;
-    if (v == FRB_KERNEL_AUTO || v == FRB_KERNEL_DEFER6) v = sparse_is_safe(cfg) ? FRB_KERNEL_DEFER6 : FRB_KERNEL_DENSE6;
-    if (v == FRB_KERNEL_STREAM6) v = sparse_is_safe(cfg) ? FRB_KERNEL_STREAM6 : FRB_KERNEL_DENSE6;
+    if (v == FRB_KERNEL_AUTO || v == FRB_KERNEL_DEFER6) v = deferred_is_safe(cfg) ? FRB_KERNEL_DEFER6 : FRB_KERNEL_DENSE6;
     if (v == FRB_KERNEL_DENSE6 && !form6_is_exact(cfg)) v = FRB_KERNEL_STREAM7;
     plan->variant = v;
     choose_deferred_shape(cfg, &plan->defer_b, &plan->defer_nb, &plan->defer_minb);
@@ -547,17 +586,19 @@ const void *deferred_kernel_of(const Plan &plan, bool julia)
     case (B) * 100 + (NB) * 10 + (S):                                                                                             \
         return julia ? (const void *)frb::frb_iterate_deferred_kernel<true, B, NB, kDeferShapes[S].per_sm, kDeferShapes[S].threads> \
                      : (const void *)frb::frb_iterate_deferred_kernel<false, B, NB, kDeferShapes[S].per_sm, kDeferShapes[S].threads>;
-#define FRB_DEFER_CASES(B, NB)                                                                                         \
-    FRB_DEFER_CASE(B, NB, 0) FRB_DEFER_CASE(B, NB, 1) FRB_DEFER_CASE(B, NB, 2) FRB_DEFER_CASE(B, NB, 3) FRB_DEFER_CASE(B, NB, 4) \
-    FRB_DEFER_CASE(B, NB, 5)
     switch (key) {
-        FRB_DEFER_CASES(8, 1) FRB_DEFER_CASES(8, 2) FRB_DEFER_CASES(8, 4) FRB_DEFER_CASES(8, 8)
-        FRB_DEFER_CASES(16, 2) FRB_DEFER_CASES(16, 4) FRB_DEFER_CASES(16, 8)
-        FRB_DEFER_CASES(32, 2) FRB_DEFER_CASES(32, 4)
+        // what choose_deferred_shape returns without tuning: caps < 256, < 2048, the rest; one wide CTA per SM
+        FRB_DEFER_CASE(8, 1, 2) FRB_DEFER_CASE(8, 4, 2) FRB_DEFER_CASE(16, 4, 2)
+#ifdef FRB_TUNING
+        // the sweeps of profiles/*_tuning_sweeps.txt: other trip lengths with the default shape, other shapes with the default trips
+        FRB_DEFER_CASE(8, 2, 2) FRB_DEFER_CASE(8, 8, 2) FRB_DEFER_CASE(16, 2, 2) FRB_DEFER_CASE(16, 8, 2) FRB_DEFER_CASE(32, 2, 2)
+        FRB_DEFER_CASE(32, 4, 2)
+        FRB_DEFER_CASE(8, 4, 0) FRB_DEFER_CASE(8, 4, 1) FRB_DEFER_CASE(8, 4, 3) FRB_DEFER_CASE(8, 4, 4) FRB_DEFER_CASE(8, 4, 5)
+        FRB_DEFER_CASE(16, 4, 0) FRB_DEFER_CASE(16, 4, 1) FRB_DEFER_CASE(16, 4, 3) FRB_DEFER_CASE(16, 4, 4) FRB_DEFER_CASE(16, 4, 5)
+#endif
     default:
         return nullptr;
     }
-#undef FRB_DEFER_CASES
 #undef FRB_DEFER_CASE
 }
 
@@ -614,32 +655,12 @@ int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaSt
         }
         return FRB_OK;
     }
-    const int kidx = (plan.variant == FRB_KERNEL_STREAM7) ? 1 : (plan.variant == FRB_KERNEL_DENSE6 ? 0 : 2);
+    const int kidx = (plan.variant == FRB_KERNEL_STREAM7) ? 1 : 0;
     uint32_t blocks = (uint32_t)(c.sm_count * c.iter_blocks_per_sm[kidx]);
     const uint32_t needed = (p.total_chunks + warps_per_block - 1) / warps_per_block;
     blocks = std::max(1u, std::min(blocks, needed));
-    if (kidx == 0) {
-        frb::frb_iterate_stream_kernel<6><<<blocks, frb::kIterateThreads, 0, st>>>(p);
-    } else if (kidx == 1) {
-        frb::frb_iterate_stream_kernel<7><<<blocks, frb::kIterateThreads, 0, st>>>(p);
-    } else {
-        // Blocks per trip (lanes that stop early idle until the trip ends, so short pixels want short trips; the
-        // iteration cap is the only a-priori hint): measured on C1..C4, profiles/r1_tuning_sweeps.txt.
-        const bool julia = (p.algo == FRB_ALGO_JULIA);
-        int nb = p.iterations >= 2048u ? 8 : (p.iterations >= 256u ? 4 : 1);
-        if (const char *e = getenv("FRB_TUNE_NB")) nb = atoi(e);  // tuning hook (bench sweeps); 1, 4 or 8
-#define FRB_LAUNCH_SPARSE(J, NB) frb::frb_iterate_sparse_kernel<J, NB><<<blocks, frb::kIterateThreads, 0, st>>>(p)
-        if (julia) {
-            if (nb == 8) FRB_LAUNCH_SPARSE(true, 8);
-            else if (nb == 4) FRB_LAUNCH_SPARSE(true, 4);
-            else FRB_LAUNCH_SPARSE(true, 1);
-        } else {
-            if (nb == 8) FRB_LAUNCH_SPARSE(false, 8);
-            else if (nb == 4) FRB_LAUNCH_SPARSE(false, 4);
-            else FRB_LAUNCH_SPARSE(false, 1);
-        }
-#undef FRB_LAUNCH_SPARSE
-    }
+    if (kidx == 0) frb::frb_iterate_stream_kernel<6><<<blocks, frb::kIterateThreads, 0, st>>>(p);
+    else frb::frb_iterate_stream_kernel<7><<<blocks, frb::kIterateThreads, 0, st>>>(p);
     return FRB_OK;
 }
 
@@ -666,6 +687,7 @@ Slot &take_slot(DeviceCtx &c, const Plan &plan)
     slot.launches = 0;
     slot.variant = plan.variant;
     slot.shaded = false;
+    slot.stream_fallback = false;
     slot.tile_key = plan.variant == FRB_KERNEL_TILE ? plan.tile_key : 0;
     slot.host->iterations = 0;
     slot.host->lane_iterations = 0;
@@ -690,7 +712,7 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
         const uint32_t n = std::max(p.width, p.height);
         frb::frb_coord_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
         slot.launches++;
-        if (p.algo != FRB_ALGO_BARNSLEY_FERN) {
+        if (!plan.fern) {
             if (int rc = launch_iterate(c, plan, p, st)) return rc;
             slot.launches += (plan.variant == FRB_KERNEL_DEFER6 && p.records == 0u) ? 2 : 1;  // raw DEFER6 = iterate + resolve
         } else {
@@ -714,14 +736,12 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
 }
 
 // True when a blocking host-destination render should go through the streaming finisher (frb_stream.cuh): the deferred
-// kernel, an image format and enough pixels for the second kernel to pay for itself.  FRB_TUNE_STREAM=0 disables it (the older
-// paths remain).  Device destinations (frb_render_device_async) are not streamed: there is no copy to hide, the finisher's
+// kernel, an image format and enough pixels for the second kernel to pay for itself.  Device destinations (frb_render_device_async) are not streamed: there is no copy to hide, the finisher's
 // FP64 work competes with K1c's either way (measured: 4.84 ms fused shade vs 5.1-5.4 ms streamed on C2), and pipelined
 // asynchronous frames would need one set of control words per frame in flight.
 bool want_streamed(const Plan &plan)
 {
-    if (const char *e = getenv("FRB_TUNE_STREAM"))
-        if (atoi(e) == 0) return false;
+    if (!tuning().stream || plan.fern) return false;
     return plan.variant == FRB_KERNEL_DEFER6 && plan.p.format != 0 && plan.npix >= (256u << 10) && plan.p.rows >= 64u;
 }
 
@@ -753,13 +773,12 @@ int enqueue_streamed(DeviceCtx &c, Plan &plan, uint8_t *dst, cudaStream_t st, Sl
     ctl.gen = reinterpret_cast<const uint32_t *>(p.stats + 11);
     ctl.started = reinterpret_cast<uint32_t *>(p.stats + 12);
     ctl.gen_value = p.stream_gen;
-    ctl.gen_polls = 20000u;  // ~20 ms (polls of ~1 us): K0 normally follows within microseconds
-    if (const char *e = getenv("FRB_TUNE_STREAMGENPOLLS")) ctl.gen_polls = (uint32_t)std::max(0, atoi(e));  // 0: test the fallback
+    ctl.gen_polls = (uint32_t)std::max(0, tuning().stream_gen_polls);  // ~20 ms (polls of ~1 us): K0 normally follows within microseconds
     ctl.nwarps = nwarps;
     // ~256 Kpx per slab: small enough that the last slab (the only exposed one) is a few microseconds of shading and copying,
     // large enough to give every finisher CTA a block or two
     uint32_t slab_rows = (uint32_t)std::max<uint64_t>(16u, ((256u << 10) / std::max(p.width, 1u) + 15u) & ~15u);
-    if (const char *e = getenv("FRB_TUNE_STREAMROWS")) slab_rows = (uint32_t)std::max(16, (atoi(e) + 15) & ~15);
+    if (tuning().stream_rows > 0) slab_rows = (uint32_t)std::max(16, (tuning().stream_rows + 15) & ~15);
     ctl.slab_rows = slab_rows;
     {
         // bound on one wait, in polls of >= 2 us: a few seconds plus a generous allowance for the slab's own work, so that it
@@ -767,8 +786,7 @@ int enqueue_streamed(DeviceCtx &c, Plan &plan, uint8_t *dst, cudaStream_t st, Sl
         const uint64_t work = (uint64_t)slab_rows * p.width * (uint64_t)std::max(p.iterations, 1u);
         ctl.max_polls = (uint32_t)std::min<uint64_t>((2u << 20) + (work >> 22), 0x7fffffffu);
     }
-    int per_sm = 1;
-    if (const char *e = getenv("FRB_TUNE_STREAMCTAS")) per_sm = std::min(8, std::max(1, atoi(e)));
+    const int per_sm = std::min(8, std::max(1, tuning().stream_ctas));
     // The finisher goes first and depends on nothing (it sleeps on the generation word until K0 has run), so that its CTAs are
     // resident before — older than — K1c's.  Frames alternate between the two auxiliary streams so that the next frame's
     // finisher can take its seat while this frame is still running.
@@ -815,21 +833,22 @@ uint8_t *device_alias_of_host(const void *host)
 // anything but stream order and events.  `host_out` should be pinned for the copies to be asynchronous.
 // Copies the shard's local rows [r0, r1) (r0 a multiple of the band height) from `src` to the host.  band_pitch == 0: the
 // destination is the shard's own compact image.  Otherwise the destination is a whole frame in which this shard's band b starts
-// at host_out + b * band_pitch (interleaved bands of kDefaultBandRows rows, frb_render with device = -1): one strided copy for the
-// full bands, one more for a partial last band.
-int copy_rows_out(uint8_t *host_out, size_t band_pitch, const uint8_t *src, uint32_t r0, uint32_t r1, size_t row_bytes, cudaStream_t cs)
+// at host_out + b * band_pitch (interleaved bands of band_rows rows: frb_render with device = -1, frb_render_bands): one strided
+// copy for the full bands, one more for a partial last band.
+int copy_rows_out(uint8_t *host_out, size_t band_pitch, uint32_t band_rows, const uint8_t *src, uint32_t r0, uint32_t r1, size_t row_bytes,
+                  cudaStream_t cs)
 {
     if (r1 <= r0) return FRB_OK;
     if (band_pitch == 0) {
         CU(cudaMemcpyAsync(host_out + (size_t)r0 * row_bytes, src, (size_t)(r1 - r0) * row_bytes, cudaMemcpyDeviceToHost, cs));
         return FRB_OK;
     }
-    const size_t band_bytes = row_bytes * kDefaultBandRows;
-    const uint32_t b0 = r0 / kDefaultBandRows;
-    const uint32_t full = (r1 - r0) / kDefaultBandRows;
+    const size_t band_bytes = row_bytes * band_rows;
+    const uint32_t b0 = r0 / band_rows;
+    const uint32_t full = (r1 - r0) / band_rows;
     uint8_t *dst0 = host_out + (size_t)b0 * band_pitch;
     if (full > 0) CU(cudaMemcpy2DAsync(dst0, band_pitch, src, band_bytes, band_bytes, full, cudaMemcpyDeviceToHost, cs));
-    const uint32_t rest = (r1 - r0) - full * kDefaultBandRows;
+    const uint32_t rest = (r1 - r0) - full * band_rows;
     if (rest > 0)
         CU(cudaMemcpyAsync(dst0 + (size_t)full * band_pitch, src + (size_t)full * band_bytes, (size_t)rest * row_bytes, cudaMemcpyDeviceToHost, cs));
     return FRB_OK;
@@ -848,22 +867,17 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
     frb::frb_coord_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
     slot.launches++;
     CU(cudaEventRecord(c.ev_fork, st));
-    // Equal slabs (multiples of 16 rows keep 16-byte alignment).  Slabs that shrink towards the end of the frame (weights n,
-    // n-1, ..., 1, so that the exposed last shade + copy is small; FRB_TUNE_SLABEQ=0) were measured no better: C2 5.267 vs
-    // 5.244 ms, C3 1.711 vs 1.632 ms, C4 210.5 vs 210.8 ms.
-    const bool equal_slabs = !(getenv("FRB_TUNE_SLABEQ") && atoi(getenv("FRB_TUNE_SLABEQ")) == 0);
-    // measured on C2 (profiles/r1_tuning_sweeps.txt): overlapped slabs 5.555 ms, pipelined 5.58-5.78 ms, unsliced 5.60 ms
-    const bool pipeline = getenv("FRB_TUNE_SLABMODE") ? atoi(getenv("FRB_TUNE_SLABMODE")) == 2 : false;
-    const uint32_t wsum = (uint32_t)(nslabs * (nslabs + 1) / 2);
+    // Equal slabs (multiples of 16 rows keep 16-byte alignment), alternating between the two auxiliary streams so that their
+    // kernels overlap freely.  Measured and rejected (profiles/r1_tuning_sweeps.txt): slabs that shrink towards the end of the
+    // frame (C2 5.267 vs 5.244 ms, C3 1.711 vs 1.632, C4 210.5 vs 210.8); kernels on one stream with the copies on the other
+    // (C2 5.58-5.78 vs 5.555 ms).
     int s = 0;
     for (uint32_t r0 = 0; r0 < p.rows; ++s) {
-        uint32_t rows_per = equal_slabs ? (p.rows + nslabs - 1) / nslabs
-                                        : (uint32_t)(((uint64_t)p.rows * (uint32_t)std::max(nslabs - s, 1) + wsum - 1) / wsum);
+        uint32_t rows_per = (p.rows + nslabs - 1) / nslabs;
         rows_per = std::max(16u, (rows_per + 15u) & ~15u);
-        // pipeline: kernels of all slabs in order on aux[0], copies on aux[1] behind per-slab events.
-        // otherwise: slabs alternate between the two streams and their kernels overlap freely.
-        cudaStream_t ks = pipeline ? c.aux[0] : c.aux[s & 1];
-        cudaStream_t cs = pipeline ? c.aux[1] : ks;
+        if (band_pitch != 0) rows_per = (rows_per + p.band_rows - 1) / p.band_rows * p.band_rows;  // slabs of whole bands
+        cudaStream_t ks = c.aux[s & 1];
+        cudaStream_t cs = ks;
         if (s < 2) CU(cudaStreamWaitEvent(c.aux[s & 1], c.ev_fork, 0));
         const uint32_t r1 = (s >= nslabs - 1) ? p.rows : std::min(p.rows, r0 + rows_per);
         RenderParams it = p;  // iterate: global pixel indexing, its own chunk range and queue counter
@@ -886,11 +900,7 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
             launch_shade(c, sh, ks);
             slot.launches += 2;
         }
-        if (pipeline) {
-            CU(cudaEventRecord(c.ev_slab[s % 16], ks));
-            CU(cudaStreamWaitEvent(cs, c.ev_slab[s % 16], 0));
-        }
-        if (int rc = copy_rows_out(host_out, band_pitch, sh.out, r0, r1, (size_t)p.width * p.format, cs)) return rc;
+        if (int rc = copy_rows_out(host_out, band_pitch, p.band_rows, sh.out, r0, r1, (size_t)p.width * p.format, cs)) return rc;
         r0 = r1;
     }
     for (int i = 0; i < 2; ++i) {
@@ -917,7 +927,7 @@ int finish_enqueue(DeviceCtx &c, Slot &slot, cudaStream_t st)
 int harvest(DeviceCtx &c, Slot &slot, FrbStats *out, double total_ms)
 {
     CU(cudaEventSynchronize(slot.ev_end));
-    if ((uint32_t)slot.host->stream_status != 0u)
+    if ((uint32_t)slot.host->stream_status != 0u && !slot.stream_fallback)
         return fail(FRB_ERR_CUDA, "the streaming finisher gave up waiting for the iterate kernel (frb_stream.cuh: stream_wait)");
     FrbStats s = {};
     s.pixels = slot.pixels;
@@ -950,8 +960,11 @@ double now_ms()
 }
 
 // One blocking render of one shard on one device into a host buffer (RGB/RGBA) and/or raw host buffers.
+// framed = false: `host_out` receives the shard's own compact image (its rows in increasing y).
+// framed = true:  `host_out` is the WHOLE frame and the shard's bands go to their place in it (band b of the shard starts at
+//                 ((b * count + index) * band_rows) rows) — how several devices, or several processes, assemble one image.
 int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t format, uint8_t *host_out, size_t out_len,
-                    uint32_t *host_iters, double *host_z)
+                    uint32_t *host_iters, double *host_z, bool framed = false)
 {
     const double t0 = now_ms();
     DeviceCtx *c = get_ctx(dev);
@@ -960,49 +973,69 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
     CU(cudaSetDevice(dev));
     Plan plan;
     if (int rc = make_plan(*c, cfg, sh, format, &plan)) return rc;
+    const size_t row_bytes = (size_t)cfg.width * format;
+    const size_t band_bytes = row_bytes * plan.p.band_rows;
+    if (sh.count <= 1) framed = false;  // the whole frame is its own compact image
     if (format != 0) {
-        if (out_len < plan.out_bytes) return fail(FRB_ERR_INVALID, "output buffer too small: %zu < %zu bytes", out_len, plan.out_bytes);
+        const size_t need = framed ? row_bytes * cfg.height : plan.out_bytes;
+        if (out_len < need) return fail(FRB_ERR_INVALID, "output buffer too small: %zu < %zu bytes", out_len, need);
         if (plan.out_bytes && !host_out) return fail(FRB_ERR_INVALID, "null output buffer");
         if (int rc = ensure(c->b().out, c->b().out_cap, plan.out_bytes + 64)) return rc;
     }
+    // where band 0 of the shard starts, and the distance between two of its bands (0 = compact)
+    uint8_t *const dst0 = framed ? host_out + (size_t)sh.index * band_bytes : host_out;
+    const size_t band_pitch = framed ? (size_t)sh.count * band_bytes : 0;
     Slot *slot = nullptr;
     // Large RGB/RGBA frames go out in row slabs so that the device->host copy hides under the iterations.
     // The tile kernel's frames are short (tens of microseconds a megapixel), so the copy dominates from ~0.5 Mpx on.
     const bool tile = plan.variant == FRB_KERNEL_TILE;
-    const bool sliced = format != 0 && !host_iters && !host_z && plan.variant != FRB_KERNEL_SIMPLE &&
-                        cfg.algo != FRB_ALGO_BARNSLEY_FERN && plan.npix >= (tile ? (1u << 19) : (4u << 20)) && plan.p.rows >= 256u &&
-                        !getenv("FRB_TUNE_NOSLAB");
+    const bool image_only = format != 0 && !host_iters && !host_z && !plan.fern;
+    const bool sliced = image_only && plan.variant != FRB_KERNEL_SIMPLE && plan.npix >= (tile ? (1u << 19) : (4u << 20)) &&
+                        plan.p.rows >= 256u && !tuning().no_slab;
     uint8_t *alias = nullptr;
-    if (format != 0 && !host_iters && !host_z && want_streamed(plan)) {
+    if (image_only && want_streamed(plan) && (!framed || ((band_bytes & 15u) == 0 && row_bytes < (1ull << 32)))) {
         alias = device_alias_of_host(host_out);
         if (alias && (reinterpret_cast<uintptr_t>(alias) & 15u) != 0) alias = nullptr;  // the shade stores are 16-byte vectors
     }
     if (alias) {
-        // pinned destination: the finisher writes the image into the caller's buffer while the iterate kernel runs
+        // pinned destination: the finisher writes the image into the caller's buffer while the iterate kernel runs; with a
+        // framed destination through strided output addressing (RenderParams::out_band_q) — no device image, no copy
+        if (framed) {
+            plan.p.out_band_q = (uint32_t)(band_bytes >> 4);
+            plan.p.out_band_gap = (unsigned long long)(sh.count - 1) * band_bytes;
+            plan.p.out_off = 0;
+            alias += (size_t)sh.index * band_bytes;
+        }
         if (int rc = enqueue_streamed(*c, plan, alias, c->stream, &slot)) return rc;
         if (int rc = finish_enqueue(*c, *slot, c->stream)) return rc;
         CU(cudaStreamSynchronize(c->stream));
-        if ((uint32_t)slot->host->stream_started == 0u) {
+        if ((uint32_t)slot->host->stream_started == 0u || (uint32_t)slot->host->stream_status != 0u) {
             // No finisher CTA saw the frame start (a profiler serialising kernels, or > 20 ms of other work ahead of this
-            // frame): the records are all there, shade them now with the ordinary kernel and copy the image out.
+            // frame), or one gave up waiting part-way (a co-tenant holding the iterate kernel back): the provisional records
+            // are all in device memory, so shade them now with the ordinary kernel and copy the image out.
             RenderParams sp = plan.p;
             sp.out = c->b().out;
+            sp.out_band_q = 0u;
+            sp.out_off = 0;
+            CU(cudaMemsetAsync(sp.stats, 0, sizeof(unsigned long long), c->stream));  // the iteration total is summed again
             launch_shade(*c, sp, c->stream);
             slot->launches++;
+            slot->stream_fallback = true;
             CU(cudaEventRecord(slot->ev_shade, c->stream));
-            CU(cudaMemcpyAsync(host_out, c->b().out, plan.out_bytes, cudaMemcpyDeviceToHost, c->stream));
+            if (int rc = copy_rows_out(dst0, band_pitch, plan.p.band_rows, c->b().out, 0u, plan.p.rows, row_bytes, c->stream)) return rc;
             CU(cudaMemcpyAsync(slot->host, c->b().stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, c->stream));
         }
     } else if (sliced) {
         // every slab is one more persistent launch (~0.1 ms of ramp and tail) but exposes a smaller last copy: 4 slabs up to
         // 32 Mpx, 8 up to 64 Mpx, 16 beyond (C2 5.24 ms with 4; C4 213.5 / 211.4 / 210.5 ms with 4 / 8 / 16)
         int nslabs = plan.npix >= (64u << 20) ? 16 : (plan.npix >= (32u << 20) ? 8 : 4);
-        if (const char *e = getenv("FRB_TUNE_SLABS")) nslabs = std::min(16, std::max(1, atoi(e)));
-        if (int rc = enqueue_sliced(*c, plan, host_out, nslabs, &slot)) return rc;
+        if (tuning().slabs > 0) nslabs = std::min(16, tuning().slabs);
+        if (int rc = enqueue_sliced(*c, plan, dst0, nslabs, &slot, band_pitch)) return rc;
     } else {
         if (int rc = enqueue(*c, plan, c->b().out, c->stream, &slot)) return rc;
         if (plan.npix > 0) {
-            if (format != 0) CU(cudaMemcpyAsync(host_out, c->b().out, plan.out_bytes, cudaMemcpyDeviceToHost, c->stream));
+            if (format != 0)
+                if (int rc = copy_rows_out(dst0, band_pitch, plan.p.band_rows, c->b().out, 0u, plan.p.rows, row_bytes, c->stream)) return rc;
             if (host_iters) CU(cudaMemcpyAsync(host_iters, c->b().iters, plan.npix * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
             if (host_z) CU(cudaMemcpyAsync(host_z, c->b().zfinal, plan.npix * sizeof(double2), cudaMemcpyDeviceToHost, c->stream));
         }
@@ -1025,42 +1058,71 @@ thread_local uint64_t tl_async_count = 0;
 // start ~35 us x g late (plan, ~10 launches and event records per device): at 8 GPUs the last shard of a 5 ms frame started
 // 0.28 ms after the first.  Each device therefore has a persistent worker that plans, enqueues, waits and harvests its own
 // shard; the caller runs device 0's share itself and joins the rest.  Workers are created on first use, parked on a condition
-// variable in between, and joined by frb_shutdown.
+// variable in between (after a short spin), and joined by frb_shutdown.
 struct DeviceWorker {
     std::thread th;
     std::mutex m;
     std::condition_variable cv;
     std::function<void()> job;
-    bool has_job = false, done = true, stop = false;
+    // `state` is the fast path: 0 = idle, 1 = job posted, 2 = running.  A worker that has just finished a job spins on it for a
+    // short while before parking on the condition variable, so that during a burst of frames (an animation, an interactive
+    // drag, a benchmark loop) the next shard starts within a microsecond instead of a futex wake-up (~20-50 us, comparable
+    // to the launch sequence of a whole shard).
+    std::atomic<int> state{0};
+    bool stop = false;
+    static constexpr int kSpinUs = 300;
 
     void loop()
     {
-        std::unique_lock<std::mutex> lk(m);
         for (;;) {
-            cv.wait(lk, [&] { return has_job || stop; });
-            if (stop) return;
-            std::function<void()> j = std::move(job);
-            has_job = false;
-            lk.unlock();
-            j();
-            lk.lock();
-            done = true;
+            // spin, then park
+            const auto t0 = std::chrono::steady_clock::now();
+            bool have = false;
+            while (!have) {
+                if (state.load(std::memory_order_acquire) == 1) {
+                    have = true;
+                    break;
+                }
+                if (std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(kSpinUs)) break;
+#if defined(__x86_64__)
+                __builtin_ia32_pause();
+#endif
+            }
+            if (!have) {
+                std::unique_lock<std::mutex> lk(m);
+                cv.wait(lk, [&] { return state.load(std::memory_order_acquire) == 1 || stop; });
+                if (stop) return;
+            }
+            state.store(2, std::memory_order_relaxed);
+            job();
+            {
+                std::lock_guard<std::mutex> lk(m);  // pairs with wait(): the store is not missed between its check and its sleep
+                state.store(0, std::memory_order_release);
+            }
             cv.notify_all();
         }
     }
+    // one job at a time per worker; the previous one has been waited for (frb_render joins every worker before it returns)
     void submit(std::function<void()> j)
     {
-        std::unique_lock<std::mutex> lk(m);
-        cv.wait(lk, [&] { return done; });  // one job at a time per device
+        wait();
         job = std::move(j);
-        has_job = true;
-        done = false;
+        {
+            std::lock_guard<std::mutex> lk(m);
+            state.store(1, std::memory_order_release);
+        }
         cv.notify_all();
     }
     void wait()
     {
+        for (int i = 0; i < 2000; ++i) {
+            if (state.load(std::memory_order_acquire) == 0) return;
+#if defined(__x86_64__)
+            __builtin_ia32_pause();
+#endif
+        }
         std::unique_lock<std::mutex> lk(m);
-        cv.wait(lk, [&] { return done; });
+        cv.wait(lk, [&] { return state.load(std::memory_order_acquire) == 0; });
     }
 };
 DeviceWorker *g_workers[kMaxDevices] = {};
@@ -1094,26 +1156,33 @@ void stop_workers_locked()
 
 std::vector<int> active_devices()
 {
-    std::vector<int> v;
+    std::vector<int> v, list;
     int n;
     uint32_t mask;
     {
         std::lock_guard<std::mutex> lk(g_mu);
         n = device_count_locked();
         mask = g_device_mask;
+        list = g_device_list;
     }
+    if (!list.empty()) return list;  // frb_init_list
     for (int d = 0; d < n; ++d)
         if (mask == 0 || (mask >> d) & 1u) v.push_back(d);
-    // Test hook: FRB_TUNE_FAKE_DEVICES=k lists the first device k times, so that the multi-device paths (sharding, strided
-    // gather, per-device workers) run — shard after shard — on a box with a single GPU.
-    if (const char *e = getenv("FRB_TUNE_FAKE_DEVICES")) {
-        const int k = std::min(atoi(e), kMaxDevices);
-        if (k > 1 && !v.empty()) v.assign((size_t)k, v[0]);
-    }
     return v;
 }
 
 }  // namespace
+
+// frb_last_error() for the other translation units of the library (frb_shared.cu)
+int frb_internal_fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    return fail(code, "%s", buf);
+}
 
 // ============================================================ C ABI ============================================================
 
@@ -1208,6 +1277,31 @@ int frb_device_count(void)
     return device_count_locked();
 }
 
+// Creates the context of device d and loads the code of the kernels an ordinary frame launches (CUDA would otherwise do it at
+// their first launch, tens of milliseconds into the first render): tables, shade, finisher, tile, and the default shapes of the
+// deferred kernel.
+static int warm_device(int d)
+{
+    DeviceCtx *c = get_ctx(d);
+    if (!c) return tl_code;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(d));
+    const void *common[] = {(const void *)frb::frb_coord_tables_kernel, (const void *)frb::frb_shade_kernel,
+                            (const void *)frb::frb_finish_stream_kernel, (const void *)frb::frb_iterate_tile_kernel<6>,
+                            (const void *)frb::frb_resolve_kernel, (const void *)frb::frb_sum_iterations_kernel};
+    for (const void *k : common)
+        if (int rc = preload_kernel(*c, k)) return rc;
+    for (uint32_t it : {64u, 1000u, 4000u})
+        for (int julia = 0; julia < 2; ++julia) {
+            FrbConfig probe = {};
+            probe.iterations = it;
+            Plan pl = {};
+            choose_deferred_shape(probe, &pl.defer_b, &pl.defer_nb, &pl.defer_minb);
+            if (int rc = preload_kernel(*c, deferred_kernel_of(pl, julia != 0))) return rc;
+        }
+    return FRB_OK;
+}
+
 int frb_init(uint32_t device_mask)
 {
     int n = frb_device_count();
@@ -1215,31 +1309,65 @@ int frb_init(uint32_t device_mask)
     bool any = false;
     for (int d = 0; d < n; ++d) {
         if (device_mask != 0 && !((device_mask >> d) & 1u)) continue;
-        DeviceCtx *c = get_ctx(d);
-        if (!c) return tl_code;
+        if (int rc = warm_device(d)) return rc;
         any = true;
-        // load the code of the kernels an ordinary frame launches (CUDA would otherwise do it at their first launch, tens of
-        // milliseconds into the first render): tables, shade, finisher, tile, and the default shapes of the deferred kernel
-        std::lock_guard<std::mutex> lk(c->mu);
-        CU(cudaSetDevice(d));
-        const void *common[] = {(const void *)frb::frb_coord_tables_kernel, (const void *)frb::frb_shade_kernel,
-                                (const void *)frb::frb_finish_stream_kernel, (const void *)frb::frb_iterate_tile_kernel<6>,
-                                (const void *)frb::frb_resolve_kernel, (const void *)frb::frb_sum_iterations_kernel};
-        for (const void *k : common)
-            if (int rc = preload_kernel(*c, k)) return rc;
-        for (uint32_t it : {64u, 1000u, 4000u})
-            for (int julia = 0; julia < 2; ++julia) {
-                FrbConfig probe = {};
-                probe.iterations = it;
-                Plan pl = {};
-                choose_deferred_shape(probe, &pl.defer_b, &pl.defer_nb, &pl.defer_minb);
-                if (int rc = preload_kernel(*c, deferred_kernel_of(pl, julia != 0))) return rc;
-            }
     }
     if (!any) return fail(FRB_ERR_INVALID, "device mask 0x%x selects none of the %d devices", device_mask, n);
     std::lock_guard<std::mutex> lk(g_mu);
     g_device_mask = device_mask;
+    g_device_list.clear();
     return FRB_OK;
+}
+
+int frb_init_list(const int32_t *devices, uint32_t n)
+{
+    const int have = frb_device_count();
+    if (have == 0) return fail(FRB_ERR_NO_DEVICE, "no usable CUDA device; this library has no CPU path");
+    if (!devices || n == 0 || n > (uint32_t)kMaxDevices) return fail(FRB_ERR_INVALID, "device list of %u entries (1..%d)", n, kMaxDevices);
+    for (uint32_t i = 0; i < n; ++i) {
+        if (devices[i] < 0 || devices[i] >= have) return fail(FRB_ERR_INVALID, "device %d out of range [0, %d)", devices[i], have);
+        if (int rc = warm_device(devices[i])) return rc;
+    }
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_device_list.assign(devices, devices + n);
+    g_device_mask = 0;
+    return FRB_OK;
+}
+
+int frb_set_tuning(const char *name, int64_t value)
+{
+    if (!name) return fail(FRB_ERR_INVALID, "null tuning name");
+#ifdef FRB_TUNING
+    using Field = int Tuning::*;
+    struct Entry {
+        const char *name;
+        Field field;
+    };
+    static const Entry table[] = {
+        {"defer_b", &Tuning::defer_b},       {"defer_nb", &Tuning::defer_nb},
+        {"defer_shape", &Tuning::defer_shape}, {"chunk", &Tuning::chunk},
+        {"fast_shade", &Tuning::fast_shade}, {"tile_max", &Tuning::tile_max},
+        {"stream", &Tuning::stream},         {"stream_gen_polls", &Tuning::stream_gen_polls},
+        {"stream_rows", &Tuning::stream_rows}, {"stream_ctas", &Tuning::stream_ctas},
+        {"slabs", &Tuning::slabs},           {"no_slab", &Tuning::no_slab},
+        {"stage", &Tuning::stage},           {"copy_threads", &Tuning::copy_threads},
+        {"end_chunk", &Tuning::end_chunk},   {"pool", &Tuning::pool},
+    };
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (strcmp(name, "reset") == 0) {
+        g_tuning = Tuning{};
+        return FRB_OK;
+    }
+    for (const Entry &e : table)
+        if (strcmp(name, e.name) == 0) {
+            g_tuning.*(e.field) = (int)value;
+            return FRB_OK;
+        }
+    return fail(FRB_ERR_INVALID, "unknown tuning knob '%s'", name);
+#else
+    (void)value;
+    return fail(FRB_ERR_INVALID, "this is a product build: tuning knob '%s' is not settable (build libfrb_tune.so with -DFRB_TUNING)", name);
+#endif
 }
 
 void frb_shutdown(void)
@@ -1251,11 +1379,12 @@ void frb_shutdown(void)
         g_ctx[d] = nullptr;
     }
     g_device_mask = 0;
+    g_device_list.clear();
 }
 
 int frb_set_kernel_variant(uint32_t variant)
 {
-    if (variant > FRB_KERNEL_TILE) return fail(FRB_ERR_INVALID, "unknown kernel variant %u", variant);
+    if (variant > FRB_KERNEL_TILE || variant == 1u) return fail(FRB_ERR_INVALID, "unknown kernel variant %u", variant);
     tl_variant = variant;
     // also forgets the tile-kernel feedback (make_plan / harvest), so that a caller comparing kernels starts from a known state
     std::lock_guard<std::mutex> lk(g_mu);
@@ -1423,6 +1552,16 @@ int frb_render_counts(const FrbConfig *cfg, const FrbShard *shard, uint32_t *ite
     return render_blocking(*cfg, s, device < 0 ? 0 : device, 0, nullptr, 0, iters, zfinal);
 }
 
+int frb_render_bands(const FrbConfig *cfg, const FrbShard *shard, uint8_t *frame, size_t frame_len, uint32_t format, int device)
+{
+    if (!cfg) return fail(FRB_ERR_INVALID, "null config");
+    if (format != FRB_RGB24 && format != FRB_RGBA32) return fail(FRB_ERR_INVALID, "unknown pixel format %u", format);
+    const FrbShard s = shard ? *shard : whole_frame();
+    const size_t need = (size_t)cfg->width * cfg->height * format;
+    if (frame_len < need) return fail(FRB_ERR_INVALID, "frame buffer too small: %zu < %zu bytes", frame_len, need);
+    return render_blocking(*cfg, s, device < 0 ? 0 : device, format, frame, frame_len, nullptr, nullptr, true);
+}
+
 int frb_render(const FrbConfig *cfg, uint8_t *out, size_t out_len, uint32_t format, int device)
 {
     if (!cfg) return fail(FRB_ERR_INVALID, "null config");
@@ -1431,8 +1570,8 @@ int frb_render(const FrbConfig *cfg, uint8_t *out, size_t out_len, uint32_t form
     if (out_len < need) return fail(FRB_ERR_INVALID, "output buffer too small: %zu < %zu bytes", out_len, need);
     if (device >= 0) return render_blocking(*cfg, whole_frame(), device, format, out, out_len, nullptr, nullptr);
 
-    // device = -1: interleaved 16-row bands over all initialised devices, one stream per device, strided gather
-    // straight into the caller's image.  No collective: shards are independent.
+    // device = -1: interleaved 16-row bands over all initialised devices, every device writing (pinned destination) or copying
+    // its bands straight into the caller's image.  No collective: shards are independent.
     const std::vector<int> devs = active_devices();
     if (devs.empty()) return fail(FRB_ERR_NO_DEVICE, "no usable CUDA device; this library has no CPU path");
     if (devs.size() == 1 || cfg->height <= kDefaultBandRows)
@@ -1446,72 +1585,18 @@ int frb_render(const FrbConfig *cfg, uint8_t *out, size_t out_len, uint32_t form
         FrbStats stats = {};
     };
     std::vector<Part> parts(G);
-    const size_t row_bytes = (size_t)cfg->width * format;
     const uint32_t variant = tl_variant;  // the caller's kernel override travels to the workers
-    // Shard g on device devs[g]: plan, enqueue, copy out, wait, harvest.  Band b of this device lands at
-    // out + (b * G + g) * band_bytes; large shards go out slab by slab under the iterations (enqueue_sliced).
-    auto render_part = [&](uint32_t g) -> int {
-        DeviceCtx *cp = get_ctx(devs[g]);
-        if (!cp) return tl_code;
-        DeviceCtx &c = *cp;
-        std::lock_guard<std::mutex> lk(c.mu);
-        CU(cudaSetDevice(c.dev));
-        Plan plan;
-        const FrbShard sh = {g, G, kDefaultBandRows, 0u};
-        if (int rc = make_plan(c, *cfg, sh, format, &plan)) return rc;
-        if (int rc = ensure(c.b().out, c.b().out_cap, plan.out_bytes + 64)) return rc;
-        const size_t band_bytes = row_bytes * kDefaultBandRows;
-        uint8_t *dst0 = out + (size_t)g * band_bytes;
-        const bool tile = plan.variant == FRB_KERNEL_TILE;
-        const bool sliced = plan.variant != FRB_KERNEL_SIMPLE && plan.npix >= (tile ? (1u << 19) : (4u << 20)) && plan.p.rows >= 256u &&
-                            !getenv("FRB_TUNE_NOSLAB");
-        Slot *slot = nullptr;
-        // Pinned destination: the streaming finisher writes this shard's bands straight into the caller's frame (strided output
-        // addressing, RenderParams::out_band_q) while the iterate kernel runs — no device image, no copy.
-        uint8_t *alias = nullptr;
-        if (want_streamed(plan) && row_bytes < (1ull << 32)) {
-            alias = device_alias_of_host(out);
-            if (alias && (reinterpret_cast<uintptr_t>(alias) & 15u) != 0) alias = nullptr;
-        }
-        if (alias) {
-            plan.p.out_band_q = (uint32_t)(band_bytes >> 4);
-            plan.p.out_band_gap = (unsigned long long)(G - 1) * band_bytes;
-            plan.p.out_off = 0;
-            if (int rc = enqueue_streamed(c, plan, alias + (size_t)g * band_bytes, c.stream, &slot)) return rc;
-            if (int rc = finish_enqueue(c, *slot, c.stream)) return rc;
-            CU(cudaStreamSynchronize(c.stream));
-            if ((uint32_t)slot->host->stream_started == 0u) {
-                // no finisher CTA saw the frame start (render_blocking has the same fallback): shade compactly, copy out
-                RenderParams sp = plan.p;
-                sp.out = c.b().out;
-                sp.out_band_q = 0u;
-                sp.out_off = 0;
-                launch_shade(c, sp, c.stream);
-                slot->launches++;
-                CU(cudaEventRecord(slot->ev_shade, c.stream));
-                if (int rc = copy_rows_out(dst0, (size_t)G * band_bytes, c.b().out, 0u, plan.p.rows, row_bytes, c.stream)) return rc;
-                CU(cudaMemcpyAsync(slot->host, c.b().stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, c.stream));
-            }
-        } else if (sliced) {
-            int nslabs = plan.npix >= (64u << 20) ? 16 : (plan.npix >= (32u << 20) ? 8 : 4);
-            if (const char *e = getenv("FRB_TUNE_SLABS")) nslabs = std::min(16, std::max(1, atoi(e)));
-            if (int rc = enqueue_sliced(c, plan, dst0, nslabs, &slot, (size_t)G * band_bytes)) return rc;
-        } else {
-            if (int rc = enqueue(c, plan, c.b().out, c.stream, &slot)) return rc;
-            if (int rc = copy_rows_out(dst0, (size_t)G * band_bytes, c.b().out, 0u, plan.p.rows, row_bytes, c.stream)) return rc;
-        }
-        if (int rc = finish_enqueue(c, *slot, c.stream)) return rc;
-        CU(cudaStreamSynchronize(c.stream));
-        return harvest(c, *slot, &parts[g].stats, 0.0);
-    };
+    // shard g on device devs[g]: plan, enqueue, wait, harvest — on that device's own host thread
     auto run_part = [&](uint32_t g) {
         tl_variant = variant;
-        parts[g].rc = render_part(g);
+        const FrbShard sh = {g, G, kDefaultBandRows, 0u};
+        parts[g].rc = render_blocking(*cfg, sh, devs[g], format, out, out_len, nullptr, nullptr, true);
         if (parts[g].rc != FRB_OK) parts[g].err = tl_error;
+        else parts[g].stats = tl_stats;
     };
     std::vector<DeviceWorker *> workers(G, nullptr);
     for (uint32_t g = 1; g < G; ++g) {
-        workers[g] = get_worker(devs[g]);
+        workers[g] = get_worker(g);  // one worker per SHARD slot: a device listed twice gets two (they serialise on its mutex)
         workers[g]->submit([&run_part, g] { run_part(g); });
     }
     run_part(0);

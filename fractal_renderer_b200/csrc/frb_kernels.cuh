@@ -365,7 +365,6 @@ frb_iterate_stream_kernel(const __grid_constant__ RenderParams p)
 
 }  // namespace frb
 
-#include "frb_sparse.cuh"    // K1b: sparse escape checks, positions of the last block recorded in registers
 #include "frb_deferred.cuh"  // K1c + K1r: the default — no recorded positions, escapes resolved by a second pass
 
 namespace frb {

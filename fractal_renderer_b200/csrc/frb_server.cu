@@ -15,6 +15,7 @@
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <random>
 #include <string>
 #include <thread>
 #include <utility>
@@ -97,9 +98,16 @@ struct Server {
     std::thread thread;
 };
 
+// What the reference's render thread calls: get_image (src/gui.rs:60), which dispatches on the algorithm (src/lib.rs:254-320).
+// Mandelbrot | Julia -> the per-pixel path; BarnsleyFern -> the chaos game with rayon's thread count and a fresh entropy seed.
 int default_renderer(const FrbConfig *cfg, uint8_t *rgba, size_t len, void *user)
 {
     const int device = (int)(intptr_t)user;
+    if (cfg->algo == FRB_ALGO_BARNSLEY_FERN) {
+        std::random_device rd;  // SmallRng::from_entropy (src/lib.rs:428)
+        const uint64_t seed = ((uint64_t)rd() << 32) ^ (uint64_t)rd();
+        return frb_render_fern(cfg, 0u, seed, nullptr, rgba, len, FRB_RGBA32, device < 0 ? 0 : device);
+    }
     return frb_render(cfg, rgba, len, FRB_RGBA32, device);
 }
 

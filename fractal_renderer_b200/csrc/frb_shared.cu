@@ -1,0 +1,210 @@
+// frb_shared.cu — frb_shared_frame_*: one host image shared by the processes of a one-process-per-GPU job.
+//
+// The reference collects the rows of one image into one Vec<RGB> (src/lib.rs:256-267).  With one process per GPU that "collect"
+// would be a gather; here it is no step at all: the image lives in POSIX shared memory, every rank maps it and registers the
+// mapping with CUDA (page-locked, portable), and each rank's frb_render_bands writes its interleaved bands straight into it —
+// by the streaming finisher over PCIe while the iterations run.  The header page in front of the image carries a
+// sense-reversing barrier so that "the whole frame is on the host" costs a few cache-line transfers, not a collective.
+#include "../../include/frb.h"
+
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <chrono>
+#include <cerrno>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <thread>
+
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+int frb_internal_fail(int code, const char *fmt, ...);  // frb_api.cu: sets frb_last_error() of the calling thread
+
+namespace {
+
+constexpr uint64_t kMagic = 0x46524253484d3031ull;  // "FRBSHM01"
+constexpr size_t kHeaderBytes = 4096;
+
+struct Header {
+    std::atomic<uint64_t> magic;   // written last by rank 0: the frame is ready to be attached
+    uint64_t bytes;
+    uint32_t ranks;
+    uint32_t pad;
+    alignas(64) std::atomic<uint32_t> arrived;
+    alignas(64) std::atomic<uint32_t> sense;
+    alignas(64) std::atomic<uint32_t> attached;  // ranks that have mapped the frame (rank 0 may unlink the name once all have)
+};
+static_assert(sizeof(Header) <= kHeaderBytes, "header page");
+static_assert(std::atomic<uint32_t>::is_always_lock_free && std::atomic<uint64_t>::is_always_lock_free, "atomics in shared memory");
+
+struct Frame {
+    std::string name;
+    Header *hdr = nullptr;
+    uint8_t *data = nullptr;
+    size_t map_bytes = 0;
+    uint32_t ranks = 1, rank = 0;
+    uint32_t local_sense = 0;
+    bool pinned = false;
+};
+
+void cpu_relax()
+{
+#if defined(__x86_64__)
+    __builtin_ia32_pause();
+#endif
+}
+
+}  // namespace
+
+extern "C" {
+
+FrbSharedFrame *frb_shared_frame_open(const char *name, size_t bytes, uint32_t ranks, uint32_t rank)
+{
+    if (!name || name[0] != '/' || strlen(name) < 2 || strchr(name + 1, '/')) {
+        frb_internal_fail(FRB_ERR_INVALID, "shared frame name must look like \"/frb-job\"");
+        return nullptr;
+    }
+    if (ranks == 0 || rank >= ranks) {
+        frb_internal_fail(FRB_ERR_INVALID, "rank %u of %u", rank, ranks);
+        return nullptr;
+    }
+    const size_t page = 4096;
+    const size_t map_bytes = kHeaderBytes + ((bytes + page - 1) / page) * page;
+    int fd = -1;
+    if (rank == 0) {
+        shm_unlink(name);  // a stale frame of a crashed job
+        fd = shm_open(name, O_CREAT | O_EXCL | O_RDWR, 0600);
+        if (fd < 0) {
+            frb_internal_fail(FRB_ERR_INVALID, "shm_open(%s, create): %s", name, strerror(errno));
+            return nullptr;
+        }
+        if (ftruncate(fd, (off_t)map_bytes) != 0) {
+            frb_internal_fail(FRB_ERR_INVALID, "ftruncate(%s, %zu): %s", name, map_bytes, strerror(errno));
+            close(fd);
+            shm_unlink(name);
+            return nullptr;
+        }
+    } else {
+        // rank 0 creates; wait for the name, then for its size, then (below) for the magic
+        const auto t0 = std::chrono::steady_clock::now();
+        for (;;) {
+            fd = shm_open(name, O_RDWR, 0600);
+            if (fd >= 0) {
+                struct stat st;
+                if (fstat(fd, &st) == 0 && (size_t)st.st_size >= map_bytes) break;
+                close(fd);
+                fd = -1;
+            }
+            if (std::chrono::steady_clock::now() - t0 > std::chrono::seconds(30)) {
+                frb_internal_fail(FRB_ERR_INVALID, "shared frame %s did not appear within 30 s (is rank 0 running?)", name);
+                return nullptr;
+            }
+            std::this_thread::sleep_for(std::chrono::milliseconds(2));
+        }
+    }
+    void *m = mmap(nullptr, map_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    close(fd);
+    if (m == MAP_FAILED) {
+        frb_internal_fail(FRB_ERR_INVALID, "mmap(%s, %zu): %s", name, map_bytes, strerror(errno));
+        if (rank == 0) shm_unlink(name);
+        return nullptr;
+    }
+    Frame *f = new (std::nothrow) Frame();
+    if (!f) {
+        munmap(m, map_bytes);
+        return nullptr;
+    }
+    f->name = name;
+    f->hdr = static_cast<Header *>(m);
+    f->data = static_cast<uint8_t *>(m) + kHeaderBytes;
+    f->map_bytes = map_bytes;
+    f->ranks = ranks;
+    f->rank = rank;
+    if (rank == 0) {
+        // fresh shared memory is zero-filled: arrived = sense = attached = 0
+        f->hdr->bytes = bytes;
+        f->hdr->ranks = ranks;
+        f->hdr->magic.store(kMagic, std::memory_order_release);
+    } else {
+        const auto t0 = std::chrono::steady_clock::now();
+        while (f->hdr->magic.load(std::memory_order_acquire) != kMagic) {
+            if (std::chrono::steady_clock::now() - t0 > std::chrono::seconds(30)) {
+                frb_internal_fail(FRB_ERR_INVALID, "shared frame %s was never initialised by rank 0", name);
+                munmap(m, map_bytes);
+                delete f;
+                return nullptr;
+            }
+            std::this_thread::sleep_for(std::chrono::milliseconds(1));
+        }
+        if (f->hdr->bytes != bytes || f->hdr->ranks != ranks) {
+            frb_internal_fail(FRB_ERR_INVALID, "shared frame %s is %llu bytes for %u ranks, not %zu for %u", name,
+                              (unsigned long long)f->hdr->bytes, f->hdr->ranks, bytes, ranks);
+            munmap(m, map_bytes);
+            delete f;
+            return nullptr;
+        }
+    }
+    // touch every page now (first-touch faults belong to set-up, not to the first frame), then pin if a device is there
+    for (size_t o = 0; o < map_bytes - kHeaderBytes; o += page) reinterpret_cast<volatile uint8_t *>(f->data)[o] |= 0;
+    if (frb_device_count() > 0 && bytes > 0) {
+        if (cudaHostRegister(f->data, map_bytes - kHeaderBytes, cudaHostRegisterPortable) == cudaSuccess) f->pinned = true;
+        else cudaGetLastError();
+    }
+    f->hdr->attached.fetch_add(1, std::memory_order_acq_rel);
+    return reinterpret_cast<FrbSharedFrame *>(f);
+}
+
+uint8_t *frb_shared_frame_data(FrbSharedFrame *h)
+{
+    Frame *f = reinterpret_cast<Frame *>(h);
+    return f ? f->data : nullptr;
+}
+
+int frb_shared_frame_pinned(FrbSharedFrame *h)
+{
+    Frame *f = reinterpret_cast<Frame *>(h);
+    return f && f->pinned ? 1 : 0;
+}
+
+int frb_shared_frame_barrier(FrbSharedFrame *h)
+{
+    Frame *f = reinterpret_cast<Frame *>(h);
+    if (!f) return frb_internal_fail(FRB_ERR_INVALID, "null shared frame");
+    if (f->ranks == 1) return FRB_OK;
+    Header *hd = f->hdr;
+    const uint32_t my = f->local_sense ^ 1u;
+    f->local_sense = my;
+    if (hd->arrived.fetch_add(1, std::memory_order_acq_rel) + 1 == f->ranks) {
+        hd->arrived.store(0, std::memory_order_relaxed);
+        hd->sense.store(my, std::memory_order_release);
+        return FRB_OK;
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    for (uint32_t spins = 0; hd->sense.load(std::memory_order_acquire) != my; ++spins) {
+        if (spins < 20000u) {
+            cpu_relax();
+        } else {
+            std::this_thread::yield();
+            if ((spins & 1023u) == 0 && std::chrono::steady_clock::now() - t0 > std::chrono::seconds(60))
+                return frb_internal_fail(FRB_ERR_INVALID, "shared frame barrier: rank %u waited 60 s for the others", f->rank);
+        }
+    }
+    return FRB_OK;
+}
+
+void frb_shared_frame_close(FrbSharedFrame *h)
+{
+    Frame *f = reinterpret_cast<Frame *>(h);
+    if (!f) return;
+    if (f->pinned && cudaHostUnregister(f->data) != cudaSuccess) cudaGetLastError();
+    if (f->rank == 0) shm_unlink(f->name.c_str());  // the mappings of the other ranks stay valid until they unmap
+    munmap(f->hdr, f->map_bytes);
+    delete f;
+}
+
+}  // extern "C"

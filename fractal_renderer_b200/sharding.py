@@ -1,7 +1,11 @@
-"""Host-side plumbing for one-process-per-GPU runs (torchrun): which rows a rank owns and how the compact shard images
-are put back together.  The data path has NO collective (shards are independent); the gather below is
-host-side assembly for callers that want the whole frame on rank 0, and works with any torch.distributed backend
-(`gloo` in the CPU tests, `nccl` with device tensors on the GPUs)."""
+"""Host-side plumbing for one-process-per-GPU runs (torchrun): which rows a rank owns and how the shards become ONE image.
+The data path has NO collective (shards are independent).  Two ways to the whole frame:
+
+  * `render_into_shared_frame` — the production path: the frame lives in POSIX shared memory that every rank maps and pins
+    (`SharedFrame`, frb_shared_frame_*); each rank's frb_render_bands writes its interleaved bands straight into it and a
+    barrier in the frame's header says "complete".  No gather step, no second copy; this is what bench.py times at N > 1.
+  * `render_distributed` — compact shards sent point to point to rank 0 and assembled there; works with any
+    torch.distributed backend (`gloo` in the CPU tests) for callers whose ranks do not share a host."""
 from __future__ import annotations
 
 from typing import Callable, Optional
@@ -33,6 +37,20 @@ def assemble(parts: list[np.ndarray], height: int, band_rows: int = BAND_ROWS) -
         assert len(rows) == part.shape[0], (r, len(rows), part.shape)
         out[rows] = part
     return out
+
+
+def render_into_shared_frame(config: Config, frame, rank: int, world: int, render_bands: Optional[Callable] = None, fmt: int = 3,
+                             device: int = 0, band_rows: int = BAND_ROWS) -> np.ndarray:
+    """Every rank calls this with the same `frame` (a SharedFrame of >= H*W*fmt bytes): renders the rank's shard into its place
+    and returns the (H, W, fmt) view of the complete image once ALL ranks have written theirs.  `render_bands(config, shard,
+    frame_array, fmt, device)` defaults to the GPU call (frb_render_bands); tests inject a CPU stand-in."""
+    if render_bands is None:
+        from . import render_bands as gpu_render_bands
+
+        render_bands = gpu_render_bands
+    render_bands(config, rank_shard(rank, world, band_rows), frame.array, fmt, device)
+    frame.barrier()
+    return frame.array[: config.height * config.width * fmt].reshape(config.height, config.width, fmt)
 
 
 def render_distributed(config: Config, render_shard: Callable[[Config, Shard], np.ndarray], dist=None,

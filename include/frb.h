@@ -72,6 +72,29 @@ typedef struct FrbConfig {
     FrbImaginary julia_set;
 } FrbConfig;
 
+/* Layout checks: a binding that mirrors these structs (#[repr(C)] in rust/ffi.rs, ctypes in the Python package) must agree with
+ * every offset below; a mismatch is a compile error on the C side too. */
+#if defined(__cplusplus) && __cplusplus >= 201103L
+#define FRB_STATIC_ASSERT(cond, msg) static_assert(cond, msg)
+#elif defined(__STDC_VERSION__) && __STDC_VERSION__ >= 201112L
+#define FRB_STATIC_ASSERT(cond, msg) _Static_assert(cond, msg)
+#else
+#define FRB_STATIC_ASSERT(cond, msg)
+#endif
+FRB_STATIC_ASSERT(sizeof(FrbImaginary) == 16, "FrbImaginary is two doubles");
+FRB_STATIC_ASSERT(sizeof(FrbRGB) == 3, "FrbRGB is three packed bytes (the memory image of calc::RGB)");
+FRB_STATIC_ASSERT(sizeof(FrbConfig) == 104, "FrbConfig is 104 bytes");
+FRB_STATIC_ASSERT(offsetof(FrbConfig, algo) == 0 && offsetof(FrbConfig, width) == 4 && offsetof(FrbConfig, height) == 8 &&
+                      offsetof(FrbConfig, iterations) == 12,
+                  "FrbConfig: algo, width, height, iterations");
+FRB_STATIC_ASSERT(offsetof(FrbConfig, limit) == 16 && offsetof(FrbConfig, stable_limit) == 24, "FrbConfig: limit, stable_limit");
+FRB_STATIC_ASSERT(offsetof(FrbConfig, pos) == 32 && offsetof(FrbConfig, scale) == 48 && offsetof(FrbConfig, exposure) == 64,
+                  "FrbConfig: pos, scale, exposure");
+FRB_STATIC_ASSERT(offsetof(FrbConfig, inside) == 72 && offsetof(FrbConfig, smooth) == 73 && offsetof(FrbConfig, primary_color) == 74 &&
+                      offsetof(FrbConfig, secondary_color) == 77,
+                  "FrbConfig: inside, smooth, primary_color, secondary_color");
+FRB_STATIC_ASSERT(offsetof(FrbConfig, color_weight) == 80 && offsetof(FrbConfig, julia_set) == 88, "FrbConfig: color_weight, julia_set");
+
 /* Fills *cfg with calc::Config::new(algo) (calc/src/lib.rs:39-69). Host-only, needs no device. */
 void frb_config_default(FrbConfig *cfg, uint32_t algo);
 /* RGB::new(r, b, g) with the reference's argument order (calc/src/lib.rs:129-131). Host-only. */
@@ -125,20 +148,21 @@ typedef struct FrbStats {
 enum {
     FRB_KERNEL_AUTO = 0,      /* TILE for short iteration caps and image formats; else DEFER6 when its preconditions hold (every
                                  sane input), else DENSE6, else STREAM7 */
-    FRB_KERNEL_STREAM6 = 1,   /* persistent lane-refill kernel, 6 FP64 instructions / iteration, one escape filter per
-                                 block of 8 iterations (needs limit >= 8 and |c| <= limit^2/2 - 3 limit: an escaped orbit
-                                 then provably keeps growing) */
+    /* 1 was STREAM6 (positions of the last block recorded in registers), retired in favour of DEFER6 */
     FRB_KERNEL_STREAM7 = 2,   /* persistent lane-refill kernel, 7 FP64 instructions / iteration, filter every
                                  iteration: exact for ANY input */
     FRB_KERNEL_SIMPLE = 3,    /* one thread per pixel, reference operation order as written (11 FP64 instructions), no
                                  queue: the on-GPU cross-check for the others */
-    FRB_KERNEL_DENSE6 = 4,    /* as STREAM6 but with the filter every iteration (small limits, short iteration caps) */
-    FRB_KERNEL_TILE = 6,      /* image formats with an iteration cap <= 384: one thread per pixel on 8x4 tiles, filter every
+    FRB_KERNEL_DENSE6 = 4,    /* persistent lane-refill kernel, 6 FP64 instructions / iteration, filter every iteration
+                                 (small or huge limits, iteration caps < 32) */
+    FRB_KERNEL_DEFER6 = 5,    /* the default: 6 FP64 instructions / iteration, ONE escape filter per block of 8-16 iterations
+                                 and nothing recorded in the loop (needs 8 <= limit <= 2^20 and |c| <= limit^2/2 - 3 limit: an
+                                 orbit that fired the filter then provably escapes at once and keeps growing); a stopped lane
+                                 stores the position at the start of its last block and a resolve pass re-runs <= 2 block - 1
+                                 iterations with the reference's test after every step */
+    FRB_KERNEL_TILE = 6       /* image formats with an iteration cap <= 384: one thread per pixel on 8x4 tiles, filter every
                                  iteration, colour in the same kernel (no records, no second kernel); exact for ANY input (it
                                  takes the 7-instruction form where the 6-instruction one is not provably exact) */
-    FRB_KERNEL_DEFER6 = 5     /* the default where STREAM6's preconditions hold: same arithmetic, nothing recorded in the
-                                 loop; a stopped lane stores the position at the start of its last block and a resolve
-                                 pass re-runs <= block+1 iterations with the reference's test after every step */
 };
 
 /* ---- lifecycle ------------------------------------------------------------------------------------------ */
@@ -148,11 +172,20 @@ int frb_device_count(void);
 /* Optional eager initialisation. device_mask bit d = use device d; 0 = all visible devices.
  * Creates contexts, streams and work queues so that the first render is not charged for them. */
 int frb_init(uint32_t device_mask);
+/* The same with an explicit list: a render with device = -1 cuts the frame into n shards and gives shard i to devices[i].
+ * A device may appear more than once (its shards are rendered one after the other) — e.g. {0, 0, 1} gives device 0 two thirds
+ * of the bands; n <= 32. */
+int frb_init_list(const int32_t *devices, uint32_t n);
 /* Releases all device and pinned memory, streams and events. Safe to call repeatedly. */
 void frb_shutdown(void);
 /* Forces the iteration kernel (FRB_KERNEL_*) for subsequent renders of this thread; FRB_KERNEL_AUTO restores
  * the default. Test/bench hook. */
 int frb_set_kernel_variant(uint32_t variant);
+/* Tuning build only (libfrb_tune.so, -DFRB_TUNING; used by the sweeps under scripts/ and by tests that force rarely taken
+ * paths): sets one of the per-frame choices the library otherwise makes itself ("defer_b", "chunk", "fast_shade", ...; "reset"
+ * restores the defaults).  The product library reads no environment variable and has no such switch: there this returns
+ * FRB_ERR_INVALID. */
+int frb_set_tuning(const char *name, int64_t value);
 
 /* ---- render: host-buffer entry points (what the reference's get_image binds to) ---------------------- */
 
@@ -166,6 +199,15 @@ int frb_render(const FrbConfig *cfg, uint8_t *out, size_t out_len, uint32_t form
 
 /* Renders one shard of the frame on `device` into a HOST buffer, compact layout (see FrbShard). */
 int frb_render_shard(const FrbConfig *cfg, const FrbShard *shard, uint8_t *out, size_t out_len,
+                     uint32_t format, int device);
+
+/* Renders one shard of the frame on `device` INTO ITS PLACE in a whole frame: `frame` addresses all width*height*format bytes
+ * (frame_len >= that) and only the rows the shard owns are written.  This is the gather of the one-process-per-GPU layout
+ * (SURVEY §8e): every process passes the same frame — a frb_shared_frame, or any memory all of them map — and its own shard,
+ * and the image is complete when all have returned; no collective, no second copy.  A pinned frame (band_rows a multiple of 16
+ * or rows of a multiple of 16 bytes) is written over PCIe while the iterations run.  frb_render(device = -1) does the same
+ * with one host thread per device. */
+int frb_render_bands(const FrbConfig *cfg, const FrbShard *shard, uint8_t *frame, size_t frame_len,
                      uint32_t format, int device);
 
 /* Parity hook: the raw result of calc::recursive (calc/src/lib.rs:245-257) per pixel of the shard
@@ -255,6 +297,25 @@ void frb_host_free(void *p);
  * per 10 MB: worth it for buffers that are rendered into many times. */
 int frb_host_register(void *p, size_t bytes);
 int frb_host_unregister(void *p);
+
+/* ---- shared frame: one host image written by several processes (one per GPU) ------------------------------------------ */
+
+/* A POSIX shared-memory image that every rank of a one-process-per-GPU job maps and pins (cudaHostRegister), so that each
+ * rank's frb_render_bands lands in the same host frame — the reference's single collected Vec<RGB> (src/lib.rs:266-267) —
+ * without a gather step.  `name` identifies the frame on this host ("/frb-<job>"), `bytes` its size, `ranks` the number of
+ * processes; rank 0 creates it, the others attach (waiting up to ~30 s for it to appear).  Works without a CUDA device (the
+ * mapping is then simply not pinned), which is how the host logic is tested on CPU.  NULL on failure (frb_last_error). */
+typedef struct FrbSharedFrame FrbSharedFrame;
+FrbSharedFrame *frb_shared_frame_open(const char *name, size_t bytes, uint32_t ranks, uint32_t rank);
+/* The image bytes (page aligned). */
+uint8_t *frb_shared_frame_data(FrbSharedFrame *frame);
+/* 1 if the mapping is page-locked (a GPU can write it directly). */
+int frb_shared_frame_pinned(FrbSharedFrame *frame);
+/* Returns when all `ranks` processes have called it the same number of times (sense-reversing counter in the shared header;
+ * spins, then yields): "the whole frame is on the host".  FRB_ERR_INVALID after ~60 s without the others. */
+int frb_shared_frame_barrier(FrbSharedFrame *frame);
+/* Unpins and unmaps; rank 0 also removes the name. */
+void frb_shared_frame_close(FrbSharedFrame *frame);
 
 /* ---- diagnostics ---------------------------------------------------------------------------------------- */
 

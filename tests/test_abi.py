@@ -99,3 +99,28 @@ def test_product_never_touches_the_oracle():
             if fn.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp")):
                 src = open(os.path.join(dirpath, fn)).read()
                 assert "oracle_binding" not in src and "calc_oracle" not in src and "libcalc_oracle" not in src, fn
+
+
+def test_product_library_has_no_tuning_hooks_and_reads_no_environment():
+    """frb_set_tuning only works in the -DFRB_TUNING build; the product library's frame path calls getenv nowhere (the one
+    getenv left is RAYON_NUM_THREADS in frb_fern_default_threads, which mirrors rayon)."""
+    L = _lib.load()
+    assert L.frb_set_tuning(b"fast_shade", 0) == _lib.FRB_ERR_INVALID
+    assert L.frb_set_tuning(b"reset", 0) == _lib.FRB_ERR_INVALID
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = open(os.path.join(root, "fractal_renderer_b200", "csrc", "frb_api.cu")).read()
+    assert src.count("getenv(") == 1 and 'getenv("RAYON_NUM_THREADS")' in src
+    for f in ("frb_server.cu", "frb_shared.cu", "frb_kernels.cuh", "frb_deferred.cuh", "frb_stream.cuh", "frb_tile.cuh"):
+        assert "getenv" not in open(os.path.join(root, "fractal_renderer_b200", "csrc", f)).read(), f
+
+
+def test_init_list_and_render_bands_fail_loudly_without_a_device():
+    L = _lib.load()
+    if L.frb_device_count() > 0:
+        pytest.skip("a GPU is visible")
+    arr = (ctypes.c_int32 * 2)(0, 0)
+    assert L.frb_init_list(arr, 2) == _lib.FRB_ERR_NO_DEVICE
+    cfg = Config.new(Algo.Mandelbrot).with_(width=32, height=32).to_c()
+    buf = (ctypes.c_uint8 * (32 * 32 * 3))()
+    sh = _lib.FrbShard(0, 2, 16, 0)
+    assert L.frb_render_bands(ctypes.byref(cfg), ctypes.byref(sh), buf, len(buf), 3, 0) == _lib.FRB_ERR_NO_DEVICE

@@ -32,6 +32,12 @@ def test_cli_defaults_differ_from_config_new():
     c = Config.cli(Algo.Mandelbrot)
     assert (c.width, c.height, c.exposure, c.pos.re) == (750, 500, 5.0, -0.6)
     assert Config.cli(Algo.Julia).pos.re == 0.0
+    # the fern keeps -0.6 (only julia resets pos_x, src/lib.rs:66-71) and takes iterations and colours from Config::new(algo)
+    f = Config.cli(Algo.BarnsleyFern)
+    assert f.pos.re == -0.6 and f.iterations == 10_000_000 and (f.width, f.height, f.exposure) == (750, 500, 5.0)
+    assert f.primary_color == Config.new(Algo.BarnsleyFern).primary_color == RGB(r=4, g=3, b=100)
+    assert f.secondary_color == RGB(r=240, g=240, b=240)
+    assert Config.cli(Algo.Julia).iterations == 50 and Config.cli(Algo.Mandelbrot).secondary_color == RGB(r=240, g=0, b=170)
 
 
 def test_hex_colour_goes_through_rgb_new():

@@ -56,6 +56,56 @@ def test_two_ranks_gloo_assemble():
     assert fr[0] == [0, 2, 4, 6, 8] and fr[1] == [1, 3, 5, 7, 9]
 
 
+def _shared_worker(rank, world, name, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_binding as ob
+    import fractal_renderer_b200 as frb
+    from fractal_renderer_b200 import configs, sharding
+
+    cfg = configs.c1().with_(width=160, height=107)
+    n = cfg.width * cfg.height * 3
+
+    def cpu_render_bands(c, shard, frame, fmt, device):  # stands in for frb_render_bands (there is no GPU here)
+        rows = shard.image_rows(c.height)
+        frame[:n].reshape(c.height, c.width, 3)[rows] = ob.render_rows(c, rows=rows, threads=1)["rgb"]
+
+    with frb.SharedFrame(name, n + 8, world, rank) as sf:
+        for rep in range(3):  # the barrier is reusable (sense reversing)
+            img = sharding.render_into_shared_frame(cfg, sf, rank, world, cpu_render_bands)
+            if rank == 0:
+                ok = bool(np.array_equal(img, ob.render_rows(cfg, threads=1)["rgb"]))
+                q.put(("shared_ok", rep, ok))
+            sf.barrier()               # nobody overwrites the frame while rank 0 is still comparing
+            sf.array[:n] = 0 if rank == 0 else sf.array[:n]
+            sf.barrier()
+        # a counter in the frame's spare bytes: every rank adds its number between barriers, 200 rounds
+        cnt = sf.array[n:n + 8].view(np.uint64)
+        for i in range(200):
+            if i % world == rank:
+                cnt[0] += 1
+            sf.barrier()
+        q.put(("count", rank, int(cnt[0])))
+        sf.barrier()
+
+
+def test_shared_frame_two_processes_assemble_one_image():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    name = f"/frb-test-{os.getpid()}"
+    procs = [ctx.Process(target=_shared_worker, args=(r, world, name, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=120) for _ in range(3 + world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(g[2] for g in got if g[0] == "shared_ok") and sum(g[0] == "shared_ok" for g in got) == 3
+    assert all(g[2] == 200 for g in got if g[0] == "count")
+    assert not os.path.exists("/dev/shm" + name)
+
+
 def test_assemble_matches_any_world():
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from fractal_renderer_b200 import sharding

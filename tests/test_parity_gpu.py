@@ -59,19 +59,18 @@ def test_small_cases_vs_oracle_and_golden(gpu, name):
     assert_parity(gpu, cfg, golden, what=name + "/auto")
 
 
-@pytest.mark.parametrize("variant", ["defer6", "stream6", "dense6", "stream7", "simple"])
+@pytest.mark.parametrize("variant", ["defer6", "dense6", "stream7", "simple"])
 @pytest.mark.parametrize("name", ["mandel_default", "mandel_iter0", "mandel_iter9", "mandel_limit1p5", "mandel_limit1e155",
                                   "mandel_limit_nan", "mandel_real_axis", "mandel_deep_subulp", "julia_default",
                                   "julia_c3_view", "C1_small", "C2_small", "C4_small"])
 def test_every_kernel_variant(gpu, name, variant):
-    """Forcing each kernel: STREAM7 and SIMPLE are exact for any input; STREAM6 is exact for these (sane) inputs."""
+    """Forcing each kernel: STREAM7 and SIMPLE are exact for any input; DEFER6 and DENSE6 are downgraded where they are not."""
     cfg = SMALL[name]
-    v = {"defer6": gpu.KERNEL_DEFER6, "stream6": gpu.KERNEL_STREAM6, "dense6": gpu.KERNEL_DENSE6, "stream7": gpu.KERNEL_STREAM7, "simple": gpu.KERNEL_SIMPLE}[variant]
+    v = {"defer6": gpu.KERNEL_DEFER6, "dense6": gpu.KERNEL_DENSE6, "stream7": gpu.KERNEL_STREAM7, "simple": gpu.KERNEL_SIMPLE}[variant]
     ref = ob.render_rows(cfg, threads=1)
     _, stats = assert_parity(gpu, cfg, ref, variant=v, what=f"{name}/{variant}")
-    # a forced kernel is downgraded (STREAM6 -> DENSE6 -> STREAM7) outside its proven domain, never run unsafely
+    # a forced kernel is downgraded (DEFER6 -> DENSE6 -> STREAM7) outside its proven domain, never run unsafely
     chain = {gpu.KERNEL_DEFER6: (gpu.KERNEL_DEFER6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7),
-             gpu.KERNEL_STREAM6: (gpu.KERNEL_STREAM6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7),
              gpu.KERNEL_DENSE6: (gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7)}.get(v, (v,))
     assert stats["kernel_variant"] in chain
     if name in ("mandel_default", "C2_small", "C4_small", "julia_default"):
@@ -148,7 +147,7 @@ def test_full_size_properties_c2_variants_agree(gpu):
     written, on the GPU) and hit the exact iteration total."""
     cfg = configs.c2()
     res = {}
-    for v in (gpu.KERNEL_DEFER6, gpu.KERNEL_STREAM6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7, gpu.KERNEL_SIMPLE):
+    for v in (gpu.KERNEL_DEFER6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7, gpu.KERNEL_SIMPLE):
         gpu.set_kernel_variant(v)
         try:
             res[v] = gpu.render_counts(cfg)
@@ -156,7 +155,7 @@ def test_full_size_properties_c2_variants_agree(gpu):
         finally:
             gpu.set_kernel_variant(gpu.KERNEL_AUTO)
     base = res[gpu.KERNEL_SIMPLE]
-    for v in (gpu.KERNEL_DEFER6, gpu.KERNEL_STREAM6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7):
+    for v in (gpu.KERNEL_DEFER6, gpu.KERNEL_DENSE6, gpu.KERNEL_STREAM7):
         assert np.array_equal(res[v][0], base[0])
         assert z_equal(res[v][1], base[1]).all()
 
@@ -266,32 +265,33 @@ def test_tile_kernel_is_the_default_for_short_caps_and_matches_the_refill_kernel
 
 # ---- the colour fast path (table log2, corrected reciprocal division) against the libdevice path ------------------------------
 
-def _render_both_shades(gpu, cfg, fmt):
-    import os
-    fast = gpu.render_shard(cfg, gpu.Shard(), fmt)
-    os.environ["FRB_TUNE_FASTSHADE"] = "0"
-    try:
-        slow = gpu.render_shard(cfg, gpu.Shard(), fmt)
-    finally:
-        del os.environ["FRB_TUNE_FASTSHADE"]
-    return fast, slow
-
-
-@pytest.mark.parametrize("name,cfg", [
+FAST_SHADE_CASES = r"""
+cases = [
     ("C1", configs.c1()),
     ("C1_it600", configs.c1().with_(iterations=600)),
     ("julia", configs.c3().with_(width=1200, height=900)),
     ("big_limit", configs.c1().with_(width=800, height=600, limit=1.0e4, iterations=300)),
     ("small_limit", configs.c1().with_(width=800, height=600, limit=1.2, stable_limit=1.2, iterations=200)),
     ("exposure", configs.c1().with_(width=800, height=600, exposure=37.5)),
-])
-def test_fast_shade_matches_libdevice_shade(gpu, name, cfg):
+]
+"""
+
+
+def test_fast_shade_matches_libdevice_shade(gpu):
     """Smooth colouring: the table log2 differs from libdevice's in the last bit or two, which moves a byte only when a
-    channel sits within ~1e-13 of an integer — allow 1 LSB on at most a handful of bytes per frame (measured: none)."""
-    fast, slow = _render_both_shades(gpu, cfg, gpu.FRB_RGB24)
+    channel sits within ~1e-13 of an integer — allow 1 LSB on at most a handful of bytes per frame (measured: none).
+    The libdevice path is only selectable in the tuning build (frb_set_tuning), hence the subprocess."""
+    from tune_run import run_with_tuning_build
+    run_with_tuning_build(FAST_SHADE_CASES + r"""
+for name, cfg in cases:
+    frb.set_tuning("fast_shade", 1)
+    fast = frb.render_shard(cfg, frb.Shard(), frb.FRB_RGB24)
+    frb.set_tuning("fast_shade", 0)
+    slow = frb.render_shard(cfg, frb.Shard(), frb.FRB_RGB24)
     d = np.abs(fast.astype(np.int16) - slow.astype(np.int16))
     assert d.max() <= 1, name
     assert int((d != 0).sum()) <= 4, f"{name}: {int((d != 0).sum())} bytes differ"
+""")
 
 
 def test_fast_shade_is_exact_without_smoothing(gpu):

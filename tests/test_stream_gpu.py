@@ -111,16 +111,32 @@ def test_unaligned_pinned_destination_falls_back(gpu):
     assert np.array_equal(buf.reshape(ref.shape), ref)
 
 
-def test_fallback_when_the_finisher_never_sees_the_frame(gpu, monkeypatch):
+def test_fallback_when_the_finisher_never_sees_the_frame(gpu):
     """Under a profiler that serialises kernels (ncu) the finisher, launched first, can never see the table kernel run: it
-    leaves after its bounded wait and the host shades with the ordinary kernel.  Forced here with a zero-poll bound."""
-    cfg = configs.c1().with_(iterations=500)
-    ref = render_ordinary(gpu, cfg, 3)
-    monkeypatch.setenv("FRB_TUNE_STREAMGENPOLLS", "0")
-    got, st = render_pinned(gpu, cfg, 3)
-    assert np.array_equal(got, ref)
-    assert st["kernel_launches"] == 4  # finisher (left at once), tables, iterate, fallback shade
-    assert st["iterations"] == gpu.last_stats()["iterations"] > 0
+    leaves after its bounded wait and the host shades with the ordinary kernel.  Forced with a zero-poll bound, which only the
+    tuning build lets one set (frb_set_tuning), hence the subprocess."""
+    from tune_run import run_with_tuning_build
+    run_with_tuning_build(r"""
+cfg = configs.c1().with_(iterations=500)
+n = cfg.width * cfg.height * 3
+ref = frb.render_shard(cfg, frb.Shard(), 3).reshape(-1)
+want_iters = frb.last_stats()["iterations"]
+for shard in (frb.Shard(), frb.Shard(1, 3, 16)):
+    buf = frb.pinned_empty(n)
+    buf[:] = 0
+    frb.set_tuning("stream_gen_polls", 20000)
+    frb.render_bands(cfg, shard, buf, 3, 0)
+    assert frb.last_stats()["kernel_launches"] == 3          # finisher, tables, iterate: streamed
+    good = buf.copy()
+    buf[:] = 0
+    frb.set_tuning("stream_gen_polls", 0)
+    frb.render_bands(cfg, shard, buf, 3, 0)
+    st = frb.last_stats()
+    assert st["kernel_launches"] == 4, st                    # finisher (left at once), tables, iterate, fallback shade
+    assert np.array_equal(buf, good)
+    if shard.count == 1:
+        assert np.array_equal(buf, ref) and st["iterations"] == want_iters
+""")
 
 
 def test_first_streamed_frame_of_each_kernel_instance_in_a_fresh_process():
