@@ -2,24 +2,33 @@
 """bench.py — headline benchmark of the escape-time path (BASELINE.json: G iter/s and ms/frame, 3000x3000 Mandelbrot
 @1e6x zoom, 1/2/4/8 B200).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload C2|C2b|C1|C3|C4]
-                    [--scaling weak|strong]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload C2|C2b|C1|C3|C4|C5]
+                    [--scaling auto|strong|weak]
 
-One "step" = one pass of the hot path over one frame (per rank).  Prints ONE JSON line (rank 0).
+A "step" is `frames_per_step` passes of the hot path over one frame (the inner repeat count is chosen so that the timed region
+lasts >= 1 s whatever K is; both are reported).  Prints ONE JSON line (rank 0).
 
-  value      G iter/s, device-resident: the frame is rendered into HBM through the C ABI's device entry point
-             (frb_render_device_async) on torch's current stream; K steps timed with CUDA events, max over ranks.
-  e2e        the same metric through the reference-facing call get_image (frb_render) with a HOST (pinned) buffer:
-             config in (104 B, travels as kernel arguments), finished RGB24 frame copied device->host every step.
-  roofline   the iterate kernel against the FP64 pipe: 10 flop per iteration as the reference writes it
-             (6 mul + 4 add, calc/src/lib.rs:88-104) over the kernel's own CUDA-event time, against the DFMA peak
-             measured on this GPU in this run (MEASURED_PEAKS.json has no FP64 entry).
-  cpu_baseline  the CPU oracle (C restatement of the reference path, OpenMP over rows like rayon) on this box's cores,
-             on a stated row-strided sample of the same frame.
+  value      G iter/s, device-resident: the frame (N > 1: this rank's interleaved 16-row bands of it) is rendered into HBM
+             through the C ABI's device entry point (frb_render_device_async) on a torch stream; timed with CUDA events, max
+             over ranks.
+  e2e        the same metric through the call the reference's get_image binds to, host buffers, copies inside the timed region.
+             N = 1: frb_render(cfg, out, ...) into a FRESH pageable allocation per frame — exactly what rust/ffi.rs does
+             (Vec::with_capacity, reference src/lib.rs:253); `e2e_pinned` beside it is the same call into a reused page-locked
+             buffer.  N > 1: every rank's frb_render_bands writes its bands into ONE shared host frame (frb_shared_frame_*) and a
+             barrier inside the timed region ends each frame when the whole image is on the host.
+  roofline   the iterate kernel against the FP64 pipe: 10 flop per iteration as the reference writes it (6 mul + 4 add,
+             calc/src/lib.rs:88-104) over the kernel's own CUDA-event time, against the DFMA peak measured on this GPU in this
+             run (MEASURED_PEAKS.json has no FP64 entry); step_frac / e2e_frac put the whole step / the e2e call in the denominator.
+  cpu_baseline  the CPU oracle (C restatement of the reference path, OpenMP over rows like rayon) on this box's cores, on a
+             stated row-strided sample of the same frame (rank 0, N = 1 only).
+  extra      c4_strong (16384^2 deep zoom cut over the N ranks, with this run's own N = 1 time for the efficiency), at N > 1
+             n1_same_run (the headline frame on one GPU of this very run), inprocess (frb_render(device = -1) from ONE process
+             over the N GPUs) and multidevice_check (bytes of the N-GPU image == bytes of the 1-GPU image).
 
---impl reference times that CPU path alone (the Rust reference cannot be built on this image: no rustc/cargo).
-N > 1 (torchrun): weak scaling = one whole frame per rank and step (frames of a sequence are independent);
-strong = one frame split into interleaved 16-row bands (rank r owns bands k % N == r).  No collective on the data path.
+N > 1 (torchrun) defaults to STRONG scaling: one frame cut into interleaved 16-row bands (rank r owns bands k % N == r), the
+partition north_star names; `--scaling weak` renders one whole frame per rank (replicas).  No collective on the data path:
+torch.distributed (NCCL) only carries the barrier and the max-over-ranks of the timing.
+--impl reference times the reference's CPU path alone (the C port of it: the Rust reference cannot be built on this image).
 """
 from __future__ import annotations
 
@@ -38,18 +47,20 @@ sys.path.insert(0, ROOT)
 
 FLOP_PER_ITER = 10  # 6 mul + 4 add/sub per loop iteration as written in the reference
 FP64_NOMINAL_TFLOPS = 37.2  # 148 SM x 64 lanes x 2 x 1.965 GHz
+MIN_TIMED_S = 1.0  # the timed region of every arm lasts at least this long
 
 
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=60)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="C2", choices=["C1", "C2", "C2b", "C3", "C4"])
-    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--workload", default="C2", choices=["C1", "C2", "C2b", "C3", "C4", "C5"])
+    ap.add_argument("--scaling", default="auto", choices=["auto", "weak", "strong"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--kernel", default="auto", choices=["auto", "stream6", "stream7", "simple", "dense6", "defer6", "tile"])
+    ap.add_argument("--no-extras", action="store_true", help="skip extra.c4_strong / n1_same_run / inprocess")
+    ap.add_argument("--kernel", default="auto", choices=["auto", "stream7", "simple", "dense6", "defer6", "tile"])
     return ap.parse_args()
 
 
@@ -59,11 +70,12 @@ WORKLOAD_TEXT = {
     "C2b": "C2b Mandelbrot 3000x3000 it4000 scale 1e6",
     "C3": "C3 Julia 4096x4096 it1000 c=(-0.7269,0.1889)",
     "C4": "C4 Mandelbrot 16384x16384 it10000 scale 1e12",
+    "C5": "C5 240-frame zoom 1e0->1e12 at 1920x1080 it10000 (a step = the whole animation)",
 }
 
 
 class ClockSampler:
-    """Samples SM clock and throttle reasons with nvidia-smi while the timed region runs."""
+    """Samples SM clock and throttle reasons with nvidia-smi while the timed regions run."""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -86,18 +98,12 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.lines.append((time.perf_counter(), line.strip()))
 
-    def stop(self, t0: float, t1: float) -> dict:
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
+    def window(self, t0: float, t1: float) -> dict:
+        """Statistics of the samples taken between t0 and t1 (perf_counter)."""
         mhz, mx, power, reasons = [], None, [], set()
-        rows = [l for (t, l) in self.lines if t0 <= t <= t1 + 0.2] or [l for (_, l) in self.lines]
-        for l in rows:
+        for (t, l) in list(self.lines):
+            if not (t0 <= t <= t1 + 0.1):
+                continue
             f = [x.strip() for x in l.split(",")]
             if len(f) < 9:
                 continue
@@ -113,11 +119,15 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(mhz) if mhz else None, "sm_max_mhz": mx, "samples": len(mhz),
                 "power_w_max": max(power) if power else None, "reasons": sorted(reasons)}
 
-
-def cpu_sample_rows(height: int, stride: int):
-    import numpy as np
-
-    return np.arange(stride // 2, height, stride, dtype=np.uint32)
+    def stop(self):
+        if self.proc is None:
+            return
+        time.sleep(0.12)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
 
 
 def host_threads() -> int:
@@ -128,33 +138,42 @@ def host_threads() -> int:
         return max(1, os.cpu_count() or 1)
 
 
+# ---------------------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (test infrastructure) as the reference's CPU implementation of the path
+# ---------------------------------------------------------------------------------------------------------------------------
+
 def time_cpu(cfg, stride: int, threads: int = 0):
-    """Oracle (OpenMP rows, like rayon) on a row-strided sample of the frame.  Returns (G iter/s, seconds, iterations)."""
+    """Oracle (OpenMP rows, like rayon) on a row-strided sample of the frame.  Returns (G iter/s, seconds, iterations, rows)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import numpy as np
     import oracle_binding as ob
 
     threads = threads or host_threads()
-
-    rows = cpu_sample_rows(cfg.height, stride)
+    rows = np.arange(stride // 2, cfg.height, stride, dtype=np.uint32)
     t = time.perf_counter()
     r = ob.render_rows(cfg, rows=rows, want_iters=False, want_z=False, want_rgb=True, threads=threads)
     dt = time.perf_counter() - t
     return r["total"] / dt / 1e9, dt, r["total"], len(rows)
 
 
-def cpu_baseline(cfg) -> dict:
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import oracle_binding as ob
+def cpu_sample_config(args, cfg_or_list):
+    """The frame the CPU arm samples: the workload's frame, or for C5 a frame from the expensive half of the animation."""
+    if args.workload == "C5":
+        return cfg_or_list[160], "frame 160 of 240"
+    return cfg_or_list, "the frame"
 
+
+def cpu_baseline(args, cfg) -> dict:
     cores = host_threads()
-    stride = 16
-    g, dt, iters, nrows = time_cpu(cfg, stride)
-    # grow the sample until it is ~10 s of CPU work (bounded: never more than the whole frame)
+    cfg1, what = cpu_sample_config(args, cfg)
+    stride = 64
+    g, dt, iters, nrows = time_cpu(cfg1, stride)
+    # grow the sample until it is several seconds of CPU work (bounded: never more than the whole frame)
     while dt < 4.0 and stride > 1:
         stride = max(1, stride // 2)
-        g, dt, iters, nrows = time_cpu(cfg, stride)
+        g, dt, iters, nrows = time_cpu(cfg1, stride)
     return {"value": round(g, 4), "unit": "G iter/s", "cores": cores, "kind": "port",
-            "sample": f"every {stride}th row of the frame ({nrows} rows x {cfg.width} px, {iters} iterations) in {dt:.2f} s; "
+            "sample": f"every {stride}th row of {what} ({nrows} rows x {cfg1.width} px, {iters} iterations) in {dt:.2f} s; "
                       "oracle/calc_oracle.c (C restatement; the Rust reference cannot be built here), OpenMP dynamic rows",
             "ms_per_frame_extrapolated": None}
 
@@ -164,31 +183,30 @@ def run_reference(args, cfg, total_iterations):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import oracle_binding as ob
-
     cores = host_threads()
+    cfg1, what = cpu_sample_config(args, cfg)
     # size the per-step sample to ~1-2 s so that K+W steps finish within a few minutes on any core count
-    stride = 16
-    g, dt, iters, nrows = time_cpu(cfg, stride)
+    stride = 64
+    g, dt, iters, nrows = time_cpu(cfg1, stride)
     while dt < 0.75 and stride > 1:
         stride //= 2
-        g, dt, iters, nrows = time_cpu(cfg, stride)
+        g, dt, iters, nrows = time_cpu(cfg1, stride)
     for _ in range(args.warmup):
-        time_cpu(cfg, stride)
+        time_cpu(cfg1, stride)
     t0 = time.perf_counter()
     tot = 0
     for _ in range(args.steps):
-        _, _, it, _ = time_cpu(cfg, stride)
+        _, _, it, _ = time_cpu(cfg1, stride)
         tot += it
     dt = time.perf_counter() - t0
     value = tot / dt / 1e9
-    sample = (f"each step = every {stride}th row of the frame ({nrows} rows x {cfg.width} px, {iters} iterations); oracle/calc_oracle.c "
+    sample = (f"each step = every {stride}th row of {what} ({nrows} rows x {cfg1.width} px, {iters} iterations); oracle/calc_oracle.c "
               "(C restatement of calc/src/lib.rs; the Rust reference cannot be built on this image), OpenMP dynamic rows = rayon rows")
     line = {
         "impl": "reference", "metric": "G iter/s", "value": round(value, 4), "unit": "G iter/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3), "higher_is_better": True,
-        "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic (the fractal itself; no RNG)",
+        "scaling": "strong" if args.gpus > 1 and args.scaling != "weak" else "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic (the fractal itself; no RNG)",
         "config": {"workload": WORKLOAD_TEXT[args.workload], "iterations_per_frame": total_iterations},
         "ms_per_frame": round(total_iterations / (value * 1e9) * 1e3, 2),
         "cpu_baseline": {"value": round(value, 4), "unit": "G iter/s", "cores": cores, "kind": "port", "sample": sample},
@@ -198,211 +216,439 @@ def run_reference(args, cfg, total_iterations):
     print(json.dumps(line), flush=True)
 
 
+# ---------------------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------------------------------
+
+class Bench:
+    def __init__(self, args):
+        import numpy as np
+        import torch
+
+        import fractal_renderer_b200 as frb
+
+        self.np, self.torch, self.frb, self.args = np, torch, frb, args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if self.world != args.gpus and self.world > 1:
+            raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={self.world}")
+        if not torch.cuda.is_available() or frb.device_count() < 1:
+            raise SystemExit("bench.py needs a B200: the product has no CPU path (use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist_mod
+
+            # NCCL may print its version banner on stdout (NCCL_DEBUG=VERSION on some boxes): keep stdout for the ONE JSON line
+            sys.stdout.flush()
+            saved_stdout = os.dup(1)
+            os.dup2(2, 1)
+            try:
+                dist_mod.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+                dist_mod.barrier()
+                torch.cuda.synchronize()
+            finally:
+                sys.stdout.flush()
+                os.dup2(saved_stdout, 1)
+                os.close(saved_stdout)
+            self.dist = dist_mod
+        frb.init(1 << self.local)
+        variant = {"auto": frb.KERNEL_AUTO, "stream7": frb.KERNEL_STREAM7, "simple": frb.KERNEL_SIMPLE, "dense6": frb.KERNEL_DENSE6,
+                   "defer6": frb.KERNEL_DEFER6, "tile": frb.KERNEL_TILE}[args.kernel]
+        frb.set_kernel_variant(variant)
+        self.stream = torch.cuda.Stream(device=self.local)  # a real (non-default) stream: launches and events go on it
+        assert self.stream.cuda_stream != 0
+        self.job = os.environ.get("MASTER_PORT", "0") + "-" + os.environ.get("TORCHELASTIC_RUN_ID", str(os.getppid()))
+        self._frames = {}
+
+    # ---- plumbing ----
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce(self, x: float, op: str) -> float:
+        if self.dist is None:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if op == "max" else self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def shared_frame(self, tag: str, nbytes: int):
+        """One host image for all ranks (POSIX shared memory, pinned by every rank); a plain pinned buffer at N = 1."""
+        if tag not in self._frames:
+            self._frames[tag] = self.frb.SharedFrame(f"/frb-bench-{self.job}-{tag}", nbytes, self.world, self.rank)
+            self._frames[tag].barrier()  # everybody has attached before anybody may close it
+        return self._frames[tag]
+
+    def close(self):
+        for f in self._frames.values():
+            f.barrier()
+            f.close()
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+
+    # ---- one workload, device-resident: K steps of R frames, CUDA events, max over ranks ----
+    def time_device(self, cfg, shard, steps, warmup, min_s=MIN_TIMED_S):
+        frb, torch = self.frb, self.torch
+        rows = shard.rows(cfg.height)
+        nbytes = rows * cfg.width * 3
+        dev_out = torch.empty(nbytes + 64, dtype=torch.uint8, device="cuda")
+
+        def one():
+            frb.render_device_async(cfg, dev_out.data_ptr(), nbytes, frb.FRB_RGB24, device=self.local, shard=shard, stream=self.stream.cuda_stream)
+
+        for _ in range(max(warmup, 3)):
+            one()
+        torch.cuda.synchronize()
+        # frames per step: from a short probe, so that K x R frames last >= min_s on the slowest rank
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(self.stream)
+        for _ in range(3):
+            one()
+        e1.record(self.stream)
+        torch.cuda.synchronize()
+        est_ms = self.reduce(e0.elapsed_time(e1) / 3.0, "max")
+        reps = max(1, int(-(-min_s * 1e3 // (steps * est_ms))))
+        self.barrier()
+        tw0 = time.perf_counter()
+        e0.record(self.stream)
+        iter_ms, shade_ms, acc = [], [], {"launches": 0, "iters": 0, "lane": 0}
+
+        def harvest(back):
+            st = frb.async_stats(back)
+            iter_ms.append(st["iterate_ms"])
+            shade_ms.append(st["shade_ms"])
+            acc["launches"] += st["kernel_launches"]
+            acc["iters"] += st["iterations"]
+            acc["lane"] += st["lane_iterations"]
+            return st
+
+        n = steps * reps
+        for k in range(n):
+            one()
+            if k > 0:  # keep one frame enqueued ahead while harvesting the previous one's statistics (host-side event wait only)
+                harvest(1)
+        e1.record(self.stream)
+        st = harvest(0)
+        self.barrier()
+        tw1 = time.perf_counter()
+        ms = self.reduce(e0.elapsed_time(e1), "max")
+        iters_all = self.reduce(float(acc["iters"]), "sum")
+        return {"ms_total": ms, "frames": n, "reps": reps, "ms_per_frame": ms / n, "g_iter_s": iters_all / (ms * 1e-3) / 1e9,
+                "iterate_ms": statistics.mean(iter_ms), "shade_ms": statistics.mean(shade_ms), "launches": acc["launches"],
+                "my_iters": acc["iters"], "lane_iters": acc["lane"], "variant": st["kernel_variant"], "window": (tw0, tw1), "nbytes": nbytes}
+
+    # ---- one workload, end to end through a host-buffer call: K steps of R frames, wall clock, max over ranks ----
+    def time_e2e(self, call, steps, warmup, min_s=MIN_TIMED_S, after=None):
+        frb = self.frb
+        for _ in range(max(warmup, 3)):
+            call()
+            if after:
+                after()
+        self.barrier()
+        t = time.perf_counter()
+        for _ in range(3):
+            call()
+            if after:
+                after()
+        est = self.reduce((time.perf_counter() - t) / 3.0, "max")
+        reps = max(1, int(-(-min_s // (steps * est))))
+        n = steps * reps
+        self.barrier()
+        t0 = time.perf_counter()
+        iters = launches = 0
+        for _ in range(n):
+            call()
+            s = frb.last_stats()
+            iters += s["iterations"]
+            launches += s["kernel_launches"]
+            if after:
+                after()  # N > 1: the frame ends when every rank's bands are on the host
+        t1 = time.perf_counter()
+        self.barrier()
+        secs = self.reduce(t1 - t0, "max")
+        iters_all = self.reduce(float(iters), "sum")
+        return {"s_total": secs, "frames": n, "reps": reps, "ms_per_frame": secs / n * 1e3, "g_iter_s": iters_all / secs / 1e9,
+                "launches": launches, "window": (t0, t1)}
+
+
+def run_c5(b: Bench, args, cfgs):
+    """C5: the whole 240-frame animation per step; frames round-robin over the ranks, each rank through frb_render_frames into
+    its slice of one shared host buffer (frame k at offset k * frame_bytes)."""
+    frb, np = b.frb, b.np
+    fbytes = cfgs[0].width * cfgs[0].height * 3
+    mine = list(range(b.rank, len(cfgs), b.world))
+    my_cfgs = [cfgs[k] for k in mine]
+    frame = b.shared_frame("c5", fbytes * len(cfgs))
+    # rank r's frames are not contiguous in the shared buffer: render into a pinned staging run, then place them
+    stage = frb.pinned_empty(fbytes * len(mine))
+
+    def call():
+        frb.render_frames(my_cfgs, frb.FRB_RGB24, device=b.local, out=stage)
+        for j, k in enumerate(mine):
+            frame.array[k * fbytes:(k + 1) * fbytes] = stage[j * fbytes:(j + 1) * fbytes]
+
+    steps = max(1, min(args.steps, 5))
+    res = b.time_e2e(call, steps, 1, min_s=0.0, after=frame.barrier if b.world > 1 else None)
+    return res, steps
+
+
 def main():
     args = parse()
     from fractal_renderer_b200 import configs
 
-    cfg = configs.BY_NAME[args.workload]()
-    total_iterations = configs.TOTAL_ITERATIONS[args.workload]
+    if args.workload == "C5":
+        cfg = configs.c5()
+        total_iterations = None
+    else:
+        cfg = configs.BY_NAME[args.workload]()
+        total_iterations = configs.TOTAL_ITERATIONS[args.workload]
 
     if args.impl == "reference":
-        run_reference(args, cfg, total_iterations)
+        run_reference(args, cfg, total_iterations or 0)
         return
 
-    import numpy as np
-    import torch
-
-    import fractal_renderer_b200 as frb
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus and world > 1:
-        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
-    if not torch.cuda.is_available() or frb.device_count() < 1:
-        raise SystemExit("bench.py needs a B200: the product has no CPU path (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist_mod
-
-        # NCCL may print its version banner on stdout (NCCL_DEBUG=VERSION on some boxes): keep stdout for the ONE JSON line
-        sys.stdout.flush()
-        saved_stdout = os.dup(1)
-        os.dup2(2, 1)
-        try:
-            dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
-            dist_mod.barrier()
-            torch.cuda.synchronize()
-        finally:
-            sys.stdout.flush()
-            os.dup2(saved_stdout, 1)
-            os.close(saved_stdout)
-        dist = dist_mod
-    frb.init(1 << local)
-    variant = {"auto": frb.KERNEL_AUTO, "stream6": frb.KERNEL_STREAM6, "stream7": frb.KERNEL_STREAM7, "simple": frb.KERNEL_SIMPLE, "dense6": frb.KERNEL_DENSE6, "defer6": frb.KERNEL_DEFER6, "tile": frb.KERNEL_TILE}[args.kernel]
-    frb.set_kernel_variant(variant)
-
-    shard = frb.Shard(rank, world, 16) if (world > 1 and args.scaling == "strong") else frb.Shard()
-    rows = shard.rows(cfg.height)
-    nbytes = rows * cfg.width * 3
-    dev_out = torch.empty(nbytes + 64, dtype=torch.uint8, device="cuda")
-    host_out = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
-    host_np = host_out.numpy()
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x: float) -> float:
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(x: float) -> float:
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
-
-    # FP64 peak of this GPU, measured now (rank-local; ~0.3 s)
-    peak = frb.measure_fp64_peak(local)
-
-    # a real (non-default) stream: the library launches on it and the CUDA events below are recorded on it
-    stream = torch.cuda.Stream(device=local)
-    assert stream.cuda_stream != 0
-    c_cfg, c_shard = cfg.to_c(), shard.to_c()
-
-    def step_device():
-        frb.render_device_async(cfg, dev_out.data_ptr(), nbytes, frb.FRB_RGB24, device=local, shard=shard, stream=stream.cuda_stream)
-
-    def step_e2e():
-        frb._lib.check(frb._lib.load().frb_render_shard(ctypes.byref(c_cfg), ctypes.byref(c_shard), host_np.ctypes.data,
-                                                        host_np.nbytes, frb.FRB_RGB24, local))
-
-    # ---------------- device-resident arm (`value`) ----------------
-    for _ in range(max(args.warmup, 3)):
-        step_device()
-    torch.cuda.synchronize()
+    b = Bench(args)
+    frb, np, torch = b.frb, b.np, b.torch
+    rank, world, local = b.rank, b.world, b.local
+    strong = world > 1 and args.scaling != "weak"
+    peak = frb.measure_fp64_peak(local)  # FP64 peak of this GPU, measured now (rank-local; ~0.3 s)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
         time.sleep(0.25)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    tw0 = time.perf_counter()
-    e0.record(stream)
-    iter_ms, shade_ms, launches, my_iters, lane_iters = [], [], 0, 0, 0
-    def harvest(back):
-        nonlocal launches, my_iters, lane_iters
-        st = frb.async_stats(back)
-        iter_ms.append(st["iterate_ms"])
-        shade_ms.append(st["shade_ms"])
-        launches += st["kernel_launches"]
-        my_iters += st["iterations"]
-        lane_iters += st["lane_iterations"]
-        return st
+    extra = {}
 
-    for k in range(args.steps):
-        step_device()
-        # keep one frame enqueued ahead while harvesting the previous one's statistics (host-side event wait only)
-        if k > 0:
-            harvest(1)
-    e1.record(stream)
-    st = harvest(0)
-    barrier()
-    tw1 = time.perf_counter()
-    dev_ms = max_over_ranks(e0.elapsed_time(e1))
-    clocks = sampler.stop(tw0, tw1) if rank == 0 else None
-    all_iters = sum_over_ranks(float(my_iters))
-    value = all_iters / (dev_ms * 1e-3) / 1e9
-    kernel_variant = st["kernel_variant"]
-
-    # ---------------- end-to-end arm (`e2e`): public host-buffer call, D2H inside the timed region ----------------
-    for _ in range(max(args.warmup, 3)):
-        step_e2e()
-    barrier()
-    t0 = time.perf_counter()
-    e2e_iters = 0
-    e2e_launches = 0
-    for _ in range(args.steps):
-        step_e2e()
-        s2 = frb.last_stats()
-        e2e_iters += s2["iterations"]
-        e2e_launches += s2["kernel_launches"]
-    barrier()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
-    e2e_value = sum_over_ranks(float(e2e_iters)) / e2e_s / 1e9
-
-    if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
+    if args.workload == "C5":
+        res, steps = run_c5(b, args, cfg)
+        if rank == 0:
+            sampler.stop()
+            clocks = sampler.window(*res["window"])
+            line = {"metric": "G iter/s", "value": round(res["g_iter_s"], 2), "unit": "G iter/s", "n_gpus": world, "steps": steps, "warmup": 1,
+                    "ms_per_step": round(res["s_total"] / steps * 1e3, 3), "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+                    "vs_baseline": None, "dtype": "f64", "data": "synthetic (the fractal itself: deterministic, no RNG, no dataset)",
+                    "config": {"workload": WORKLOAD_TEXT["C5"], "frames": len(cfg), "partition": "frames round-robin over the ranks" if world > 1 else "single GPU",
+                               "format": "RGB24"},
+                    "frames_per_s": round(len(cfg) * steps / res["s_total"], 2),
+                    "e2e": {"value": round(res["g_iter_s"], 2), "unit": "G iter/s", "h2d_bytes_per_step": 104 * len(cfg),
+                            "d2h_bytes_per_step": cfg[0].width * cfg[0].height * 3 * len(cfg),
+                            "api": "frb_render_frames per rank (its frames k % N == rank, dynamic in-order queue over its device), every frame copied into one shared host buffer"},
+                    "gpu_launches": res["launches"], "clocks": clocks, "roofline": None, "cpu_baseline": None if args.no_cpu_baseline else cpu_baseline(args, cfg)}
+            print(json.dumps(line), flush=True)
+        b.close()
         return
 
+    # ---------------- device-resident arm (`value`) ----------------
+    shard = frb.Shard(rank, world, 16) if strong else frb.Shard()
+    dev = b.time_device(cfg, shard, args.steps, args.warmup)
+
+    # ---------------- end-to-end arms ----------------
+    c_cfg = cfg.to_c()
+    L = frb._lib.load()
+    full_bytes = cfg.width * cfg.height * 3
+    e2e_pinned = None
+    if strong:
+        frame = b.shared_frame("main", full_bytes)
+        c_shard = shard.to_c()
+
+        def call_bands():
+            frb._lib.check(L.frb_render_bands(ctypes.byref(c_cfg), ctypes.byref(c_shard), frame.array.ctypes.data, full_bytes, frb.FRB_RGB24, local))
+
+        e2e = b.time_e2e(call_bands, args.steps, args.warmup, after=frame.barrier)
+        e2e_api = ("frb_render_bands per rank into ONE shared host frame (frb_shared_frame: POSIX shared memory pinned by every rank; the streaming "
+                   "finisher writes each rank's interleaved 16-row bands over PCIe while it iterates) + a shared-memory barrier per frame: "
+                   "the frame ends when the whole image is on the host")
+        d2h = full_bytes
+    else:
+        keep = []
+
+        def call_fresh():
+            # what rust/ffi.rs get_image_b200 does: a fresh, untouched allocation per frame (Vec::with_capacity), frb_render into it
+            out = np.empty(full_bytes, np.uint8)
+            keep[:] = [out]
+            frb._lib.check(L.frb_render(ctypes.byref(c_cfg), out.ctypes.data, full_bytes, frb.FRB_RGB24, local))
+
+        pinned = frb.pinned_empty(full_bytes)
+
+        def call_pinned():
+            frb._lib.check(L.frb_render(ctypes.byref(c_cfg), pinned.ctypes.data, full_bytes, frb.FRB_RGB24, local))
+
+        e2e = b.time_e2e(call_fresh, args.steps, args.warmup)
+        e2e_pinned = b.time_e2e(call_pinned, args.steps, args.warmup)
+        e2e_api = ("frb_render(cfg, out, len, RGB24, device) into a FRESH pageable allocation per frame (np.empty = Vec::with_capacity, as "
+                   "rust/ffi.rs get_image_b200 does; allocation and first-touch page faults inside the timed region); weak N > 1: one such frame per rank")
+        d2h = full_bytes
+
+    # ---------------- extras: evidence the driver can only get from this run ----------------
+    if not args.no_extras and args.workload in ("C2", "C2b"):
+        # (1) N > 1: the headline frame on ONE GPU of this very run (the efficiency denominator), rank 0 alone
+        if strong:
+            n1_dev = n1_e2e = None
+            if rank == 0:
+                saved = b.dist
+                b.dist = None
+                n1_dev = b.time_device(cfg, frb.Shard(), max(5, args.steps // 2), 3, min_s=0.5)
+                pin1 = frb.pinned_empty(full_bytes)
+                n1_e2e = b.time_e2e(lambda: frb._lib.check(L.frb_render(ctypes.byref(c_cfg), pin1.ctypes.data, full_bytes, frb.FRB_RGB24, local)),
+                                    max(5, args.steps // 2), 3, min_s=0.5)
+                b.dist = saved
+                extra["n1_same_run"] = {"ms_per_frame": round(n1_dev["ms_per_frame"], 4), "g_iter_s": round(n1_dev["g_iter_s"], 1),
+                                        "e2e_pinned_ms_per_frame": round(n1_e2e["ms_per_frame"], 4)}
+                extra["strong_efficiency"] = {"device_resident": round(n1_dev["ms_per_frame"] / (world * dev["ms_per_frame"]), 4),
+                                              "e2e": round(n1_e2e["ms_per_frame"] / (world * e2e["ms_per_frame"]), 4),
+                                              "note": "T1 / (N x TN), T1 measured on rank 0's GPU in this run; limiter at small shards: the tail of the frame "
+                                                      "(the last pixels handed out are full-length orbits: a fixed ~0.1 ms whatever the shard size)"}
+            frame.barrier()
+        # (2) C4 (16384^2 deep zoom): the configuration north_star's >= 85 % target is quoted on
+        c4 = configs.c4()
+        c4_bytes = c4.width * c4.height * 3
+        c4_shard = frb.Shard(rank, world, 16) if world > 1 else frb.Shard()
+        c4_frame = b.shared_frame("c4", c4_bytes)
+        c4_c, c4_s = c4.to_c(), c4_shard.to_c()
+
+        def call_c4():
+            frb._lib.check(L.frb_render_bands(ctypes.byref(c4_c), ctypes.byref(c4_s), c4_frame.array.ctypes.data, c4_bytes, frb.FRB_RGB24, local))
+
+        c4_res = b.time_e2e(call_c4, 3, 1, min_s=0.0, after=c4_frame.barrier if world > 1 else None)
+        rec = {"workload": WORKLOAD_TEXT["C4"], "partition": "one frame, interleaved 16-row bands" if world > 1 else "single GPU",
+               "ms_per_frame": round(c4_res["ms_per_frame"], 3), "g_iter_s": round(c4_res["g_iter_s"], 1), "frames_timed": c4_res["frames"],
+               "measured": "end to end: frb_render_bands per rank into one shared pinned host frame + barrier per frame (gather to host included)"}
+        if world > 1:
+            n1 = None
+            if rank == 0:
+                whole = frb.Shard().to_c()
+                t = []
+                for k in range(3):
+                    t0 = time.perf_counter()
+                    frb._lib.check(L.frb_render_bands(ctypes.byref(c4_c), ctypes.byref(whole), c4_frame.array.ctypes.data, c4_bytes, frb.FRB_RGB24, local))
+                    t.append((time.perf_counter() - t0) * 1e3)
+                n1 = min(t[1:])
+                rec["n1_ms_per_frame_same_run"] = round(n1, 3)
+                rec["efficiency"] = round(n1 / (world * c4_res["ms_per_frame"]), 4)
+            c4_frame.barrier()
+        extra["c4_strong"] = rec
+        # (3) N > 1: the in-process path — ONE process (rank 0) drives all N GPUs through frb_render(device = -1), the call a
+        # Rust get_image makes on a multi-GPU box — timed while the other ranks wait on a host-side barrier; and the check that
+        # its bytes equal the one-GPU image (C1-, C3- and C2-shaped frames).
+        if strong:
+            if rank == 0:
+                try:
+                    frb.init((1 << world) - 1)
+                    chk = {}
+                    for name, c in (("C3", configs.c3().with_(width=2048, height=1024)), ("C1", configs.c1()), ("C2", cfg)):
+                        nb = c.width * c.height * 3
+                        buf = frb.pinned_empty(nb)
+                        frb.get_image_into(c, buf, frb.FRB_RGB24, device=-1)
+                        ndev = frb.last_stats()["devices"]
+                        one = frb.render_shard(c, frb.Shard(), frb.FRB_RGB24, device=local).reshape(-1)
+                        chk[name] = bool(np.array_equal(buf, one)) and ndev == world
+                    extra["multidevice_check"] = "ok" if all(chk.values()) else f"MISMATCH {chk}"
+                    buf = frb.pinned_empty(full_bytes)
+                    for _ in range(5):
+                        frb.get_image_into(cfg, buf, frb.FRB_RGB24, device=-1)
+                    t0 = time.perf_counter()
+                    nrep = 200
+                    for _ in range(nrep):
+                        frb.get_image_into(cfg, buf, frb.FRB_RGB24, device=-1)
+                    ms = (time.perf_counter() - t0) / nrep * 1e3
+                    extra["inprocess"] = {"api": "frb_render(device = -1) from one process, one host worker per GPU, pinned destination",
+                                          "ms_per_frame": round(ms, 4), "devices": world,
+                                          "efficiency_vs_n1_same_run": round(extra["n1_same_run"]["e2e_pinned_ms_per_frame"] / (world * ms), 4)}
+                except frb.FrbError as e:  # evidence, not a reason to lose the headline line
+                    extra["multidevice_check"] = f"FAILED: {e}"
+                finally:
+                    frb.init(1 << local)
+            frame.barrier()
+            # the per-rank path of this bench, checked too: the shared frame every rank just wrote == rank 0's one-GPU image
+            call_bands()
+            frame.barrier()
+            if rank == 0:
+                one = frb.render_shard(cfg, frb.Shard(), frb.FRB_RGB24, device=local).reshape(-1)
+                extra["shared_frame_check"] = "ok" if np.array_equal(frame.array[:full_bytes], one) else "MISMATCH"
+            frame.barrier()
+
+    if rank != 0:
+        b.close()
+        return
+    sampler.stop()
+
     # ---------------- roofline of the dominant kernel (iterate) ----------------
-    it_ms = statistics.mean(iter_ms)
-    per_launch_iters = my_iters / args.steps
+    it_ms = dev["iterate_ms"]
+    per_launch_iters = dev["my_iters"] / dev["frames"]
     achieved_tflops = per_launch_iters * FLOP_PER_ITER / (it_ms * 1e-3) / 1e12
     peak_tflops = peak["dfma_per_s"] * 2 / 1e12
-    form = {frb.KERNEL_TILE: 6, frb.KERNEL_DEFER6: 6, frb.KERNEL_STREAM6: 6, frb.KERNEL_DENSE6: 6, frb.KERNEL_STREAM7: 7}.get(kernel_variant, 11)
-    kname = {frb.KERNEL_TILE: "frb_iterate_tile_kernel<6> (iterate + shade)", frb.KERNEL_DEFER6: "frb_iterate_deferred_kernel<6>", frb.KERNEL_STREAM6: "frb_iterate_sparse_kernel<6>", frb.KERNEL_DENSE6: "frb_iterate_stream_kernel<6>",
-             frb.KERNEL_STREAM7: "frb_iterate_stream_kernel<7>"}.get(kernel_variant, "frb_iterate_simple_kernel")
-    traffic = None
+    kv = dev["variant"]
+    form = {frb.KERNEL_TILE: 6, frb.KERNEL_DEFER6: 6, frb.KERNEL_DENSE6: 6, frb.KERNEL_STREAM7: 7}.get(kv, 11)
+    kname = {frb.KERNEL_TILE: "frb_iterate_tile_kernel<6> (iterate + shade)", frb.KERNEL_DEFER6: "frb_iterate_deferred_kernel<6>",
+             frb.KERNEL_DENSE6: "frb_iterate_stream_kernel<6>", frb.KERNEL_STREAM7: "frb_iterate_stream_kernel<7>"}.get(kv, "frb_iterate_simple_kernel")
+    traffic, traffic_note = None, None
     try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json"))).get(args.workload)
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json"))).get(args.workload)
         if tj and tj["kernel"] == kname and world == 1:
             traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+            traffic_note = tj.get("note")
     except (OSError, ValueError, KeyError):
         pass
+    frame_flop = (total_iterations / world if strong else total_iterations) * FLOP_PER_ITER
     roofline = {
         "bound": "fp64",
         "achieved": round(achieved_tflops, 3), "peak": round(peak_tflops, 3), "unit": "TFLOP/s",
-        "frac": round(achieved_tflops / peak_tflops, 4), "traffic": traffic,
-        "traffic_note": "DRAM bytes read+written by this kernel per launch from one ncu --set full capture (profiles/r1_traffic.json); algorithmic = 20 B/px raw result written, 0 read",
+        "frac": round(achieved_tflops / peak_tflops, 4),
+        "step_frac": round(frame_flop / (dev["ms_per_frame"] * 1e-3) / 1e12 / peak_tflops, 4),
+        "e2e_frac": round(frame_flop / (e2e["ms_per_frame"] * 1e-3) / 1e12 / peak_tflops, 4),
+        "traffic": traffic,
+        "traffic_note": traffic_note or "DRAM bytes read+written by this kernel per launch from one ncu --set full capture (profiles/r2_traffic.json)",
+        "algorithmic_bytes": cfg.width * cfg.height * 3,
+        "algorithmic_bytes_note": "3 B/px written, 0 read (SURVEY §8d); the kernel is FP64-bound: bytes say what is wasted, not what bounds it",
         "kernel": kname,
-        "kernel_ms": round(it_ms, 4), "shade_kernel_ms": round(statistics.mean(shade_ms), 4),
-        "shade_kernel_note": "frb_shade_kernel; with the defer6 iterate kernel it also resolves each pixel's provisional record (<= block+1 iterations with the reference's test)",
-        "kernel_share_of_step": round(it_ms * args.steps / dev_ms, 4) if world == 1 else None,
+        "kernel_ms": round(it_ms, 4), "shade_kernel_ms": round(dev["shade_ms"], 4),
+        "kernel_share_of_step": round(it_ms / dev["ms_per_frame"], 4),
         "peak_source": "measured in this run: frb_measure_fp64_peak DFMA stream x 2 flop (MEASURED_PEAKS.json has no FP64 entry)",
         "peak_nominal": FP64_NOMINAL_TFLOPS, "frac_of_nominal": round(achieved_tflops / FP64_NOMINAL_TFLOPS, 4),
         "fp64_instr_per_iter": form,
         "pipe_frac": round(per_launch_iters * form / (it_ms * 1e-3) / peak["dfma_per_s"], 4),
-        "lane_utilisation": round(my_iters / lane_iters, 4) if lane_iters else None,
+        "lane_utilisation": round(dev["my_iters"] / dev["lane_iters"], 4) if dev["lane_iters"] else None,
         "peak_detail": {k: round(v / 1e12, 3) for k, v in peak.items() if k.endswith("_per_s")},
         "note": "bound is the FP64 pipe (scalar recurrence, 3 B written per ~1400 iterations): HBM and tensor rooflines do not apply; "
                 "achieved counts the reference's 10 flop/iteration, the kernel issues fp64_instr_per_iter FP64 instructions per iteration "
-                "(pipe_frac = FP64 instructions issued for useful iterations / measured DFMA instruction peak)",
+                "(pipe_frac = FP64 instructions issued for useful iterations / measured DFMA instruction peak); "
+                "frac = over the iterate kernel's own time, step_frac = over the device-resident step, e2e_frac = over the e2e call",
     }
 
-    cpu = None if args.no_cpu_baseline else cpu_baseline(cfg)
-    if cpu is not None:
+    cpu = None
+    if not args.no_cpu_baseline and world == 1:
+        cpu = cpu_baseline(args, cfg)
         cpu["ms_per_frame_extrapolated"] = round(total_iterations / (cpu["value"] * 1e9) * 1e3, 1)
 
-    frames_per_step = world if args.scaling == "weak" else 1
+    w_dev, w_e2e = dev["window"], e2e["window"]
+    clocks = sampler.window(w_dev[0], w_dev[1])
+    clocks["e2e_arm"] = sampler.window(w_e2e[0], w_e2e[1])
+    frames_per_step = dev["reps"] * (world if (world > 1 and not strong) else 1)
     line = {
-        "metric": "G iter/s", "value": round(value, 2), "unit": "G iter/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": round(dev_ms / args.steps, 4), "higher_is_better": True, "scaling": args.scaling if world > 1 else "weak",
+        "metric": "G iter/s", "value": round(dev["g_iter_s"], 2), "unit": "G iter/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": round(dev["ms_total"] / args.steps, 4), "higher_is_better": True, "scaling": "strong" if strong else "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic (the fractal itself: deterministic, no RNG, no dataset)",
         "config": {
             "workload": WORKLOAD_TEXT[args.workload], "iterations_per_frame": total_iterations, "frames_per_step": frames_per_step,
-            "partition": ("one whole frame per rank" if args.scaling == "weak" else "one frame, interleaved 16-row bands per rank") if world > 1 else "single GPU",
-            "kernel": frb.KERNEL_NAMES[kernel_variant], "format": "RGB24",
-            "l2": "not flushed: no reusable input (48 KB of coordinate tables are recomputed every step); each step writes 207 MB (> 126 MB L2)",
+            "timed_region_s": round(dev["ms_total"] * 1e-3, 3),
+            "partition": ("one frame, interleaved 16-row bands" if strong else "one whole frame per rank") if world > 1 else "single GPU",
+            "kernel": frb.KERNEL_NAMES[kv], "format": "RGB24",
+            "l2": "not flushed: no reusable input (48 KB of coordinate tables are recomputed every frame); each frame writes 207 MB (> 126 MB L2)",
         },
-        "ms_per_frame": round(dev_ms / args.steps, 4),
-        "e2e": {"value": round(e2e_value, 2), "unit": "G iter/s", "h2d_bytes_per_step": 104, "d2h_bytes_per_step": nbytes + 16,
-                "ms_per_step": round(e2e_s / args.steps * 1e3, 4),
-                "api": "frb_render_shard (what get_image binds to): config struct in, finished RGB24 frame into the caller's pinned host memory (written over PCIe by the streaming finisher kernel while the iterate kernel runs)"},
-        "gpu_launches": launches,
-        "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+        "ms_per_frame": round(dev["ms_per_frame"], 4),
+        "e2e": {"value": round(e2e["g_iter_s"], 2), "unit": "G iter/s", "h2d_bytes_per_step": 104 * e2e["reps"], "d2h_bytes_per_step": (d2h + 16 * (world if strong else 1)) * e2e["reps"],
+                "ms_per_frame": round(e2e["ms_per_frame"], 4), "frames_per_step": e2e["reps"], "timed_region_s": round(e2e["s_total"], 3), "api": e2e_api},
+        "gpu_launches": dev["launches"] + e2e["launches"],
+        "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "extra": extra,
     }
+    if e2e_pinned is not None:
+        line["e2e_pinned"] = {"value": round(e2e_pinned["g_iter_s"], 2), "unit": "G iter/s", "ms_per_frame": round(e2e_pinned["ms_per_frame"], 4),
+                              "api": "the same frb_render call into a reused page-locked buffer (frb_host_alloc): written by the streaming finisher over PCIe while the iterate kernel runs"}
+        line["gpu_launches"] += e2e_pinned["launches"]
     print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
+    b.close()
 
 
 if __name__ == "__main__":

@@ -1,7 +1,7 @@
 // frb_shared.cu — frb_shared_frame_*: one host image shared by the processes of a one-process-per-GPU job.
 //
 // The reference collects the rows of one image into one Vec<RGB> (src/lib.rs:256-267).  With one process per GPU that "collect"
-// would be a gather; here it is no step at all: the image lives in POSIX shared memory, every rank maps it and registers the
+// would be a gather; here it is no step at all: the image lives in shared memory (a file in /dev/shm), every rank maps it and registers the
 // mapping with CUDA (page-locked, portable), and each rank's frb_render_bands writes its interleaved bands straight into it —
 // by the streaming finisher over PCIe while the iterations run.  The header page in front of the image carries a
 // sense-reversing barrier so that "the whole frame is on the host" costs a few cache-line transfers, not a collective.
@@ -21,6 +21,7 @@
 #include <fcntl.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
+#include <sys/statvfs.h>
 #include <unistd.h>
 
 int frb_internal_fail(int code, const char *fmt, ...);  // frb_api.cu: sets frb_last_error() of the calling thread
@@ -75,31 +76,43 @@ FrbSharedFrame *frb_shared_frame_open(const char *name, size_t bytes, uint32_t r
     }
     const size_t page = 4096;
     const size_t map_bytes = kHeaderBytes + ((bytes + page - 1) / page) * page;
+    // The frame is a file in a memory-backed directory: /dev/shm where it has room (containers often cap it at 64 MB), else /tmp.
+    static const char *const kDirs[] = {"/dev/shm", "/tmp"};
     int fd = -1;
+    std::string path;
     if (rank == 0) {
-        shm_unlink(name);  // a stale frame of a crashed job
-        fd = shm_open(name, O_CREAT | O_EXCL | O_RDWR, 0600);
+        for (const char *d : kDirs) unlink((std::string(d) + name).c_str());  // a stale frame of a crashed job
+        for (const char *d : kDirs) {
+            struct statvfs vfs;
+            if (statvfs(d, &vfs) != 0 || (uint64_t)vfs.f_bavail * vfs.f_frsize < (uint64_t)map_bytes + (64u << 20)) continue;
+            path = std::string(d) + name;
+            fd = open(path.c_str(), O_CREAT | O_EXCL | O_RDWR | O_CLOEXEC, 0600);
+            if (fd >= 0) break;
+        }
         if (fd < 0) {
-            frb_internal_fail(FRB_ERR_INVALID, "shm_open(%s, create): %s", name, strerror(errno));
+            frb_internal_fail(FRB_ERR_INVALID, "no room for a %zu-byte shared frame %s in /dev/shm or /tmp: %s", map_bytes, name, strerror(errno));
             return nullptr;
         }
-        if (ftruncate(fd, (off_t)map_bytes) != 0) {
-            frb_internal_fail(FRB_ERR_INVALID, "ftruncate(%s, %zu): %s", name, map_bytes, strerror(errno));
+        if (posix_fallocate(fd, 0, (off_t)map_bytes) != 0 && ftruncate(fd, (off_t)map_bytes) != 0) {
+            frb_internal_fail(FRB_ERR_INVALID, "cannot size %s to %zu bytes: %s", path.c_str(), map_bytes, strerror(errno));
             close(fd);
-            shm_unlink(name);
+            unlink(path.c_str());
             return nullptr;
         }
     } else {
         // rank 0 creates; wait for the name, then for its size, then (below) for the magic
         const auto t0 = std::chrono::steady_clock::now();
-        for (;;) {
-            fd = shm_open(name, O_RDWR, 0600);
-            if (fd >= 0) {
+        while (fd < 0) {
+            for (const char *d : kDirs) {
+                path = std::string(d) + name;
+                fd = open(path.c_str(), O_RDWR | O_CLOEXEC);
+                if (fd < 0) continue;
                 struct stat st;
                 if (fstat(fd, &st) == 0 && (size_t)st.st_size >= map_bytes) break;
                 close(fd);
                 fd = -1;
             }
+            if (fd >= 0) break;
             if (std::chrono::steady_clock::now() - t0 > std::chrono::seconds(30)) {
                 frb_internal_fail(FRB_ERR_INVALID, "shared frame %s did not appear within 30 s (is rank 0 running?)", name);
                 return nullptr;
@@ -111,7 +124,7 @@ FrbSharedFrame *frb_shared_frame_open(const char *name, size_t bytes, uint32_t r
     close(fd);
     if (m == MAP_FAILED) {
         frb_internal_fail(FRB_ERR_INVALID, "mmap(%s, %zu): %s", name, map_bytes, strerror(errno));
-        if (rank == 0) shm_unlink(name);
+        if (rank == 0) unlink(path.c_str());
         return nullptr;
     }
     Frame *f = new (std::nothrow) Frame();
@@ -119,7 +132,7 @@ FrbSharedFrame *frb_shared_frame_open(const char *name, size_t bytes, uint32_t r
         munmap(m, map_bytes);
         return nullptr;
     }
-    f->name = name;
+    f->name = path;
     f->hdr = static_cast<Header *>(m);
     f->data = static_cast<uint8_t *>(m) + kHeaderBytes;
     f->map_bytes = map_bytes;
@@ -202,7 +215,7 @@ void frb_shared_frame_close(FrbSharedFrame *h)
     Frame *f = reinterpret_cast<Frame *>(h);
     if (!f) return;
     if (f->pinned && cudaHostUnregister(f->data) != cudaSuccess) cudaGetLastError();
-    if (f->rank == 0) shm_unlink(f->name.c_str());  // the mappings of the other ranks stay valid until they unmap
+    if (f->rank == 0) unlink(f->name.c_str());  // the mappings of the other ranks stay valid until they unmap
     munmap(f->hdr, f->map_bytes);
     delete f;
 }

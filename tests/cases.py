@@ -61,6 +61,13 @@ def edge_cases() -> dict[str, Config]:
         "julia_tiny_im": j.with_(julia_set=Imaginary(-0.5, 1e-300)),
         "julia_c3_view": small(configs.c3(), 100, 100),
         "julia_no_smooth": j.with_(smooth=False, inside=False),
+        # Near-miss territory of the sparse escape filter: start points with |z0|^2 between S/2 and S and a Julia constant that
+        # cancels z0^2, so orbits hover around the escape radius.  limit = 2^20 with |c| = 0.49 limit^2 is the last input the
+        # deferred kernel accepts (frb_api.cu: deferred_is_safe); at limit = 1e8 the filter's truncation slack would eat the
+        # proof's margin, so that one must take the dense kernel.
+        "julia_limit_2p20_bigc": j.with_(limit=1048576.0, julia_set=Imaginary(-0.49 * 1048576.0 ** 2, 1000.0),
+                                         pos=Imaginary(0.7 * 1048576.0, 0.0), iterations=64),
+        "julia_limit1e8_bigc": j.with_(limit=1e8, julia_set=Imaginary(-5.625e15, 1e7), pos=Imaginary(7.5e7, 0.0), iterations=64),
         "fern_black": Config.new(Algo.BarnsleyFern).with_(width=20, height=10, iterations=100),
     }
     return cases

@@ -84,7 +84,8 @@ def test_auto_routes_exotic_inputs_to_form7(gpu):
                          ("mandel_limit_nan", gpu.KERNEL_STREAM7), ("mandel_huge_coords", gpu.KERNEL_STREAM7),
                          ("mandel_real_axis", gpu.KERNEL_DEFER6), ("mandel_limit2", gpu.KERNEL_DENSE6),
                          ("mandel_limit1p5", gpu.KERNEL_DENSE6), ("mandel_iter7", gpu.KERNEL_DENSE6),
-                         ("mandel_far_out", gpu.KERNEL_DEFER6), ("C4_small", gpu.KERNEL_DEFER6)]:
+                         ("mandel_far_out", gpu.KERNEL_DEFER6), ("C4_small", gpu.KERNEL_DEFER6),
+                         ("julia_limit_2p20_bigc", gpu.KERNEL_DEFER6), ("julia_limit1e8_bigc", gpu.KERNEL_DENSE6)]:
         gpu.render_counts(SMALL[name])
         assert gpu.last_stats()["kernel_variant"] == expect, name
 
@@ -296,13 +297,24 @@ for name, cfg in cases:
 
 def test_fast_shade_is_exact_without_smoothing(gpu):
     """smooth = false: no logarithm, and the corrected reciprocal division is correctly rounded, so the fast path must be
-    byte-identical — including the structured cases where count/iterations*exposure*channel lands exactly on an integer."""
-    for it, exposure in ((50, 2.0), (255, 1.0), (100, 2.55), (256, 3.0), (1000, 10.0), (77, 0.7)):
+    byte-identical to the oracle's division — including the structured cases where count/iterations*exposure*channel lands
+    exactly on an integer — and to the libdevice path (tuning build, subprocess)."""
+    cases = ((50, 2.0), (255, 1.0), (100, 2.55), (256, 3.0), (1000, 10.0), (77, 0.7))
+    for it, exposure in cases:
         cfg = configs.c1().with_(width=640, height=480, iterations=it, exposure=exposure, smooth=False)
-        fast, slow = _render_both_shades(gpu, cfg, gpu.FRB_RGBA32)
-        assert np.array_equal(fast, slow), (it, exposure)
+        fast = gpu.render_shard(cfg, gpu.Shard(), gpu.FRB_RGBA32)
         ref = ob.render_rows(cfg, threads=1)
         assert np.array_equal(fast[..., :3].reshape(-1), ref["rgb"].reshape(-1)), (it, exposure)
+    from tune_run import run_with_tuning_build
+    run_with_tuning_build(f"cases = {cases!r}" + r"""
+for it, exposure in cases:
+    cfg = configs.c1().with_(width=640, height=480, iterations=it, exposure=exposure, smooth=False)
+    frb.set_tuning("fast_shade", 1)
+    fast = frb.render_shard(cfg, frb.Shard(), frb.FRB_RGBA32)
+    frb.set_tuning("fast_shade", 0)
+    slow = frb.render_shard(cfg, frb.Shard(), frb.FRB_RGBA32)
+    assert np.array_equal(fast, slow), (it, exposure)
+""")
 
 
 def test_tile_kernel_backs_off_on_scenes_with_poor_lane_utilisation(gpu):
