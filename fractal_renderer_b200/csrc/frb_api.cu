@@ -59,6 +59,7 @@ struct Tuning {
     int copy_threads = 0;       // staging pipeline: host copy threads (0 = default)
     int end_chunk = 0;          // deferred kernel: pixels per chunk in the end phase of the queue (0 = default)
     int pool = 1;               // deferred kernel: 0 = no orbit pool (drained warps keep their lanes to the end)
+    int pool_max = 31;          //                  a drained warp with at most this many live lanes donates them (<= 31)
 };
 #ifdef FRB_TUNING
 Tuning g_tuning;
@@ -643,7 +644,37 @@ int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaSt
         const void *kfn = deferred_kernel_of(plan, julia);
         if (!kfn)
             return fail(FRB_ERR_INVALID, "no deferred kernel for block %d x %d, shape %d", plan.defer_b, plan.defer_nb, plan.defer_minb);
-        void *args[] = {const_cast<RenderParams *>(&p)};
+        // The queue of this launch (frb_deferred.cuh): rows [row0, row0 + nrows) of the shard; the last rows — about two refills
+        // of every lane of the grid — go out in short chunks so that little unstarted work is left in any warp's hands when the
+        // queue runs dry, and drained warps with few live lanes merge through the CTA's orbit pool.
+        RenderParams q = p;
+        {
+            const uint32_t row0 = p.chunks_per_row ? p.chunk_begin / p.chunks_per_row : 0u;
+            const uint32_t nrows = p.chunks_per_row ? p.total_chunks / p.chunks_per_row : 0u;
+            const uint32_t threads = (uint32_t)kDeferShapes[plan.defer_minb].threads;
+            // short chunks only pay where a pixel can be long (C2/8: 0.750 -> 0.711 ms with 4-pixel chunks and the pool; C3,
+            // cap 1000: 0.909 -> 0.942 ms — the extra queue traffic costs more than the shorter tail gains)
+            const int chunk2_default = p.iterations >= 2048u ? 4 : (int)p.chunk;
+            const uint32_t chunk2 = (uint32_t)std::max(1, std::min(tuning().end_chunk > 0 ? tuning().end_chunk : chunk2_default, (int)p.chunk));
+            const uint64_t end_px = 2ull * blocks * threads;
+            uint32_t end_rows = (uint32_t)std::min<uint64_t>((end_px + p.width - 1) / std::max(p.width, 1u), nrows / 4u);
+            if (chunk2 == p.chunk) end_rows = 0;
+            q.q_row0 = row0;
+            q.q_rows_big = nrows - end_rows;
+            q.q_nbig = q.q_rows_big * p.chunks_per_row;
+            q.q_chunk2 = chunk2;
+            q.q_cpr2 = (p.width + chunk2 - 1) / chunk2;
+            const uint64_t total = (uint64_t)q.q_nbig + (uint64_t)end_rows * q.q_cpr2;
+            if (total > 0xfffffff0ull) {  // cannot happen below 2^32 pixels with >= 1-pixel chunks on a quarter of the rows; be safe
+                q.q_rows_big = nrows;
+                q.q_nbig = nrows * p.chunks_per_row;
+                q.total_chunks = q.q_nbig;
+            } else {
+                q.total_chunks = (uint32_t)total;
+            }
+            q.q_pool_max = tuning().pool ? (uint32_t)std::min(31, std::max(0, tuning().pool_max)) : 0u;
+        }
+        void *args[] = {&q};
         CU(cudaLaunchKernel(kfn, dim3(blocks), dim3((unsigned)kDeferShapes[plan.defer_minb].threads), args, 0, st));
         // raw-result path: K1r over the rows this launch covered (with an image format the shade kernel resolves instead)
         RenderParams r = p;
@@ -1352,6 +1383,7 @@ int frb_set_tuning(const char *name, int64_t value)
         {"slabs", &Tuning::slabs},           {"no_slab", &Tuning::no_slab},
         {"stage", &Tuning::stage},           {"copy_threads", &Tuning::copy_threads},
         {"end_chunk", &Tuning::end_chunk},   {"pool", &Tuning::pool},
+        {"pool_max", &Tuning::pool_max},
     };
     std::lock_guard<std::mutex> lk(g_mu);
     if (strcmp(name, "reset") == 0) {

@@ -89,6 +89,33 @@ __device__ __forceinline__ bool deferred_trip(double &x, double &y, double &a, d
     }
 }
 
+// ---- the end of a frame ------------------------------------------------------------------------------------------------
+// Measured (profiles/r2_probe1_timeline_latency_pageable.txt): from the moment the queue runs dry to the exit of the last warp
+// a C2 frame spends 0.23 ms — whatever the size of the frame or shard, i.e. 5 % of the whole frame and 30 % of an eighth of
+// it — with the FP64 pipe draining all the while.  Two causes, two remedies:
+//  * a warp holds up to a chunk of unstarted pixels plus a prefetched chunk when the queue runs dry, each possibly a
+//    full-length orbit.  -> The last rows of the launch are handed out in SHORT chunks (RenderParams::q_chunk2), so that what
+//    a warp still holds at that moment is a few pixels, not 64.
+//  * after that, every warp keeps running until its slowest lane is done, more and more of its lanes parked: 24 warps per SM
+//    at a few live lanes each share the pipe at 72 cycles per iteration, where 2 full warps per SM sub-partition would run the
+//    same orbits at the 24-cycle latency bound of the dependent chain (scripts/latency_probe.cu).  -> Every SM sub-partition
+//    has an ORBIT POOL in shared memory: a drained warp left with at most q_pool_max live lanes pushes their orbits (position,
+//    carried squares, c, budget counter, pixel) into the pool of its sub-partition and exits; drained warps with parked lanes
+//    pop them.  Live lanes thus collect in few, full warps, evenly over the four schedulers.  A warp only donates when the
+//    parked lanes registered by the other warps of its sub-partition can take all its orbits at once — an orbit waiting in
+//    the pool makes no progress at all (first version, one pool per CTA without that rule: the tail grew from 0.18 to 0.27 ms,
+//    profiles/r2_pool_sweep1_cta_pool_rejected.txt).  All pool traffic is on the cold side, under a spin lock, after the queue is dry.
+constexpr int kPoolCap = 160;  // per sub-partition: >= (warps per sub-partition - 1) x the largest q_pool_max (31)
+
+struct OrbitPool {
+    uint32_t lock;               // 0 = free
+    uint32_t count;              // orbits in the pool (a stack)
+    uint32_t alive;              // warps of this sub-partition that have neither exited nor donated their lanes
+    uint32_t free;               // parked lanes registered by the drained warps of this sub-partition
+    double x[kPoolCap], y[kPoolCap], a[kPoolCap], b[kPoolCap], cr[kPoolCap], ci[kPoolCap];
+    uint32_t cnt[kPoolCap], pix[kPoolCap], donor[kPoolCap];
+};
+
 // CT threads per CTA, MINB resident CTAs per SM.  Warps are independent workers, so the CTA shape only matters to the warp
 // scheduler — and there it matters a lot: measured on B200 (scripts/trace_warps.py), warps of co-resident CTAs are NOT served
 // evenly.  With 3 CTAs of 8 warps per SM the oldest CTA's warps made ~4000 trips per frame, the second's ~1250 and the
@@ -100,9 +127,26 @@ __global__ void __launch_bounds__(CT, MINB)
 frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
 {
     constexpr unsigned FULL = 0xffffffffu;
+    __shared__ OrbitPool pools[4];
+    __shared__ uint32_t pool_remaining[32];  // per warp: pixels it took from the queue itself and donated, not yet recorded
     const unsigned lane = threadIdx.x & 31u;
+    const unsigned warp_in_cta = threadIdx.x >> 5;
     const unsigned lt_mask = (1u << lane) - 1u;
     const uint32_t filter_hi = p.filter_hi;
+    const uint32_t pool_max = p.q_pool_max;  // 0: no pool
+    // warps w, w + 4, w + 8, ... of a CTA run on the same SM sub-partition (scheduler): they share a pool
+    OrbitPool &pool = pools[warp_in_cta & 3u];
+    if (pool_max != 0u) {
+        if (threadIdx.x < 32u) pool_remaining[threadIdx.x] = 0u;
+        if (threadIdx.x < 4u) {
+            pools[threadIdx.x].lock = 0u;
+            pools[threadIdx.x].count = 0u;
+            pools[threadIdx.x].free = 0u;
+            pools[threadIdx.x].alive = (CT / 32 + 3 - threadIdx.x) / 4;
+        }
+        __syncthreads();  // the only CTA-wide barrier of the kernel: before any warp has work
+    }
+    uint32_t my_free = 0u;  // warp-uniform: the parked lanes this warp has registered in pool.free
 
     // Per-lane orbit.  A lane without a pixel (pix == kNoPixel) runs the zero orbit with cnt counting up from 0: it
     // cannot reach filter_hi (> 2^30) before the warp's other lanes exhaust their budgets (< 2^30).
@@ -127,15 +171,30 @@ frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
     // Watermark for the streaming finisher (frb_stream.cuh): the lowest pixel index this warp still owes a record for.
     // Published (release) whenever the warp fetched a chunk or the queue is drained, and as 0xffffffff on exit.  A stale
     // value is always a lower bound: the queue hands out increasing chunk ids, so whatever the warp takes next lies above
-    // everything it holds now.
-    uint32_t *const wm = p.wm ? p.wm + (blockIdx.x * (CT / 32) + (threadIdx.x >> 5)) : nullptr;
+    // everything it holds now.  Pixels never change watermark: an orbit donated to the pool stays covered by the warp that
+    // took it from the queue (its `origin`), which does not publish its exit before every such pixel has its record — the
+    // finisher's scan of the table is not atomic, so coverage must never move between slots.
+    uint32_t *const wm = p.wm ? p.wm + (blockIdx.x * (CT / 32) + warp_in_cta) : nullptr;
     bool fetched = false;
+    uint32_t origin = kNoPixel;  // per lane: the warp (in this CTA) whose pixel this lane runs after taking it from the pool
+    bool poll_pool = false;  // warp-uniform: drained, lanes parked, so look into the pool after every trip
 
     for (;;) {
         // ------------------------------ service (cold) ------------------------------
         // a stopped lane still holds the (a, b, cnt) that fired the filter; running lanes and idle lanes do not fire it
-        if (max3u((uint32_t)__double2hiint(a), (uint32_t)__double2hiint(b), cnt) >= filter_hi) pix = kNoPixel;  // record already written
+        if (max3u((uint32_t)__double2hiint(a), (uint32_t)__double2hiint(b), cnt) >= filter_hi) {
+            pix = kNoPixel;  // record already written
+            if (origin != kNoPixel) {
+                // a pixel taken over from the pool: tell the warp that owes it to the finisher, after the record
+                if (wm != nullptr) {
+                    __threadfence();
+                    atomicSub(&pool_remaining[origin], 1u);
+                }
+                origin = kNoPixel;
+            }
+        }
         unsigned need = __ballot_sync(FULL, pix == kNoPixel);
+        bool leave = false;
         if (need != 0u) {
             const uint32_t cnt0 = filter_hi + (uint32_t)(B - 1) - p.iterations;
             if (!drained) {
@@ -175,11 +234,22 @@ frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
                             }
                             if (lane == 0) next_chunk = atomicAdd(p.queue, 1u);
                             fetched = true;
-                            const uint32_t cg = c + p.chunk_begin;
-                            const uint32_t lr = cg / p.chunks_per_row;
-                            const uint32_t seg = cg - lr * p.chunks_per_row;
-                            cur_x = seg * p.chunk;
-                            cur_end = min(cur_x + p.chunk, p.width);
+                            // chunk -> row segment: long chunks first, the short chunks of the end phase after them
+                            uint32_t lr, x0, len;
+                            if (c < p.q_nbig) {
+                                const uint32_t r = c / p.chunks_per_row;
+                                lr = p.q_row0 + r;
+                                x0 = (c - r * p.chunks_per_row) * p.chunk;
+                                len = p.chunk;
+                            } else {
+                                const uint32_t c2 = c - p.q_nbig;
+                                const uint32_t r = c2 / p.q_cpr2;
+                                lr = p.q_row0 + p.q_rows_big + r;
+                                x0 = (c2 - r * p.q_cpr2) * p.q_chunk2;
+                                len = p.q_chunk2;
+                            }
+                            cur_x = x0;
+                            cur_end = min(x0 + len, p.width);
                             cur_rowpix = lr * p.width;
                             cur_im = __ldg(p.tab_im + local_row_to_y(p, lr));
                         }
@@ -203,14 +273,99 @@ frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
                 }
             }
             if (need != 0u) {
-                // queue drained: lanes without a pixel park on the zero orbit; the warp leaves when all are parked
-                if (need == FULL) break;
-                if (pix == kNoPixel) {
+                // Queue drained.
+                if (pool_max == 0u) {
+                    if (need == FULL) break;  // no lane holds a pixel: the warp leaves
+                } else {
+                    // One decision per service call, taken by lane 0 under the pool's lock: take orbits over, leave, or donate.
+                    const uint32_t nfree = (uint32_t)__popc(need), live = 32u - nfree;
+                    uint32_t action = 0u, k = 0u, base = 0u;  // action: 0 keep going, 1 take k orbits at base, 2 exit, 3 donate at base
+                    uint32_t reg = nfree;                      // parked lanes this warp has registered after the decision
+                    if (lane == 0) {
+                        while (atomicCAS(&pool.lock, 0u, 1u) != 0u) __nanosleep(32);
+                        const uint32_t have = *reinterpret_cast<volatile uint32_t *>(&pool.count);
+                        const uint32_t alive = *reinterpret_cast<volatile uint32_t *>(&pool.alive);
+                        const uint32_t fr = *reinterpret_cast<volatile uint32_t *>(&pool.free);
+                        if (have != 0u) {
+                            action = 1u;
+                            k = min(have, nfree);
+                            base = have - k;
+                            reg = nfree - k;
+                            *reinterpret_cast<volatile uint32_t *>(&pool.count) = base;
+                        } else if (live == 0u) {
+                            action = 2u;
+                            reg = 0u;
+                            *reinterpret_cast<volatile uint32_t *>(&pool.alive) = alive - 1u;
+                        } else if (live <= pool_max && alive > 1u && live <= fr - my_free && live <= (uint32_t)kPoolCap) {
+                            // the parked lanes of the OTHER warps of this sub-partition take all of this warp's orbits at once
+                            action = 3u;
+                            base = 0u;
+                            reg = 0u;
+                            *reinterpret_cast<volatile uint32_t *>(&pool.count) = live;
+                            *reinterpret_cast<volatile uint32_t *>(&pool.alive) = alive - 1u;
+                        }
+                        *reinterpret_cast<volatile uint32_t *>(&pool.free) = fr - my_free + reg;
+                    }
+                    my_free = __shfl_sync(FULL, reg, 0);
+                    action = __shfl_sync(FULL, action, 0);
+                    k = __shfl_sync(FULL, k, 0);
+                    base = __shfl_sync(FULL, base, 0);
+                    if (action == 1u) {
+                        const uint32_t rank = (uint32_t)__popc(need & lt_mask);
+                        if (pix == kNoPixel && rank < k) {
+                            const uint32_t i = base + rank;
+                            x = *reinterpret_cast<volatile double *>(&pool.x[i]);
+                            y = *reinterpret_cast<volatile double *>(&pool.y[i]);
+                            a = *reinterpret_cast<volatile double *>(&pool.a[i]);
+                            b = *reinterpret_cast<volatile double *>(&pool.b[i]);
+                            cr = *reinterpret_cast<volatile double *>(&pool.cr[i]);
+                            ci = *reinterpret_cast<volatile double *>(&pool.ci[i]);
+                            cnt = *reinterpret_cast<volatile uint32_t *>(&pool.cnt[i]);
+                            pix = *reinterpret_cast<volatile uint32_t *>(&pool.pix[i]);
+                            origin = *reinterpret_cast<volatile uint32_t *>(&pool.donor[i]);
+                        }
+                    } else if (action == 3u) {
+                        if (pix != kNoPixel) {
+                            const uint32_t i = base + (uint32_t)__popc(~need & lt_mask);
+                            *reinterpret_cast<volatile double *>(&pool.x[i]) = x;
+                            *reinterpret_cast<volatile double *>(&pool.y[i]) = y;
+                            *reinterpret_cast<volatile double *>(&pool.a[i]) = a;
+                            *reinterpret_cast<volatile double *>(&pool.b[i]) = b;
+                            *reinterpret_cast<volatile double *>(&pool.cr[i]) = cr;
+                            *reinterpret_cast<volatile double *>(&pool.ci[i]) = ci;
+                            *reinterpret_cast<volatile uint32_t *>(&pool.cnt[i]) = cnt;
+                            *reinterpret_cast<volatile uint32_t *>(&pool.pix[i]) = pix;
+                            *reinterpret_cast<volatile uint32_t *>(&pool.donor[i]) = origin != kNoPixel ? origin : warp_in_cta;
+                        }
+                        if (wm != nullptr) {
+                            // pixels this warp took from the queue itself stay its responsibility until they are recorded
+                            const uint32_t own = (uint32_t)__popc(__ballot_sync(FULL, pix != kNoPixel && origin == kNoPixel));
+                            if (lane == 0 && own != 0u) atomicAdd(&pool_remaining[warp_in_cta], own);
+                        }
+                    }
+                    __threadfence_block();
+                    __syncwarp();
+                    if (lane == 0) atomicExch(&pool.lock, 0u);
+                    leave = action == 2u || action == 3u;
+                    need = __ballot_sync(FULL, pix == kNoPixel);
+                    if (action == 3u) need = FULL;
+                }
+                // lanes without a pixel park on the zero orbit
+                if (!leave && pix == kNoPixel) {
                     x = y = a = b = cr = ci = 0.0;
                     cnt = 0u;
                 }
             }
         }
+        if (leave) {
+            if (wm != nullptr) {
+                // pixels this warp donated (now or earlier, as a taker that donated on) stay under its last watermark until
+                // whoever runs them has written their records
+                while (*reinterpret_cast<volatile uint32_t *>(&pool_remaining[warp_in_cta]) != 0u) __nanosleep(200);
+            }
+            break;
+        }
+        poll_pool = pool_max != 0u && drained && need != 0u;
 
         if (wm != nullptr && (fetched || drained)) {
             uint32_t low = __reduce_min_sync(FULL, pix);  // lanes without a pixel hold kNoPixel = 0xffffffff
@@ -222,15 +377,24 @@ frb_iterate_deferred_kernel(const __grid_constant__ RenderParams p)
         }
 
         // ------------------------------ hot ------------------------------
-        // Every lane enters with at least B iterations left (host: iterations >= B).  Trips repeat until some lane stopped.
+        // Every lane enters with at least B iterations left (host: iterations >= B).  Trips repeat until some lane stopped
+        // (or, for a drained warp with parked lanes, until the pool has something to take over).
         uint32_t *const rec_iters = p.iters + pix;  // parked lanes never stop, so their (wild) addresses are never used
         double2 *const rec_z = p.zfinal + pix;
         const uint32_t rec_bias = p.iterations - filter_hi - (uint32_t)(2 * B - 1);
         bool live;
-        do {
-            ++trips;
-            live = deferred_trip<B, NB>(x, y, a, b, cnt, cr, ci, filter_hi, rec_iters, rec_z, rec_bias);
-        } while (__all_sync(FULL, live));
+        if (!poll_pool) {
+            do {
+                ++trips;
+                live = deferred_trip<B, NB>(x, y, a, b, cnt, cr, ci, filter_hi, rec_iters, rec_z, rec_bias);
+            } while (__all_sync(FULL, live));
+        } else {
+            do {
+                ++trips;
+                live = deferred_trip<B, NB>(x, y, a, b, cnt, cr, ci, filter_hi, rec_iters, rec_z, rec_bias);
+                if (*reinterpret_cast<volatile uint32_t *>(&pool.count) != 0u) live = false;  // same word for every lane: uniform
+            } while (__all_sync(FULL, live));
+        }
     }
 
     if (wm != nullptr) {

@@ -59,6 +59,11 @@ struct RenderParams {
     uint32_t records;       // K2: 1 = iters/zfinal hold K1c's provisional records; resolve them while shading (local row 0 of the
                             // pointers is shard row resolve_row0)
     uint32_t stream_gen;    // K0 -> K2s: generation of this frame, published once the control words are reset (0 = not streamed)
+    // K1c's queue (frb_deferred.cuh): the launch covers local rows [q_row0, ...); the first q_nbig chunks are segments of `chunk`
+    // pixels (chunks_per_row per row, q_rows_big rows), the rest — the END PHASE of the frame — segments of q_chunk2 pixels
+    // (q_cpr2 per row).  total_chunks counts both.  q_pool_max: a drained warp with at most this many live lanes hands them to
+    // the CTA's orbit pool and leaves (0 = no pool).
+    uint32_t q_row0, q_rows_big, q_nbig, q_cpr2, q_chunk2, q_pool_max;
     // Output addressing of K2 / K2s.  out_band_q == 0: `out` is this launch's own compact image.  Otherwise `out` is where the
     // shard's band 0 starts inside a WHOLE frame shared with other devices' shards (frb_render, device = -1): compact byte offset
     // o of the shard maps to o + (o / band_bytes) * out_band_gap, band_bytes = 16 * out_band_q (one band of kDefaultBandRows rows),
