@@ -105,6 +105,9 @@ __device__ __forceinline__ bool deferred_trip(double &x, double &y, double &a, d
 //    parked lanes registered by the other warps of its sub-partition can take all its orbits at once — an orbit waiting in
 //    the pool makes no progress at all (first version, one pool per CTA without that rule: the tail grew from 0.18 to 0.27 ms,
 //    profiles/r2_pool_sweep1_cta_pool_rejected.txt).  All pool traffic is on the cold side, under a spin lock, after the queue is dry.
+//    Measured with both (profiles/r2_pool_sweep2_smsp_pools.txt): queue dry -> last warp 0.23 -> 0.13 ms, median SM 0.16 -> 0.10 ms.
+//    Also tried, no gain: retiring all but 2-3 warps per sub-partition for the last 25-400 Kpx of the frame so that late pixels
+//    run at the chain's latency bound from the start (C2 1/8: 0.716 -> 0.713-0.728 ms).
 constexpr int kPoolCap = 160;  // per sub-partition: >= (warps per sub-partition - 1) x the largest q_pool_max (31)
 
 struct OrbitPool {
