@@ -31,6 +31,11 @@ struct StreamCtl {
     uint32_t slab_rows;   // multiple of 16 (keeps every slab's first output byte 16-byte aligned)
     uint32_t max_polls;   // bound on one wait (polls of >= 2 us)
     uint32_t pad;
+    uint32_t *slab_count; // nullptr, or [nslabs] device counters (zeroed by the host): work items of the slab already shaded
+    uint32_t *slab_ready; // [nslabs] flags in mapped HOST memory: set by the CTA that shaded the slab's last item, after a system
+                          // fence — the slab's pixels are in the (host) destination; host copy threads wait on them
+    uint32_t blocks_per_slab;
+    uint32_t pad2;
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns()
@@ -171,6 +176,17 @@ frb_finish_stream_kernel(const __grid_constant__ RenderParams p, const __grid_co
         sh.zfinal = p.zfinal + pix0;
         offset_out(sh, p, pix0);
         shade_blocks(sh, stage, lg, blk, 0xffffffffffull, useful);  // exactly one block (none if blk is past a short last slab)
+        if (ctl.slab_count != nullptr) {
+            // destination = the library's pinned staging buffer (frb_api.cu: pageable destinations): tell the host's copy threads
+            // when the slab is complete.  Counting happens in device memory (atomics on mapped host memory are not something to
+            // lean on); only the plain "ready" store crosses PCIe, behind the pixels of every CTA that counted before this one.
+            __threadfence_system();  // this thread's pixels before the count
+            __syncthreads();
+            if (threadIdx.x == 0 && atomicAdd(ctl.slab_count + slab, 1u) + 1u == ctl.blocks_per_slab) {
+                __threadfence_system();
+                *reinterpret_cast<volatile uint32_t *>(ctl.slab_ready + slab) = 1u;
+            }
+        }
     }
     shade_publish_useful(p, useful);
 #ifdef FRB_STREAM_TRACE

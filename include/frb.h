@@ -78,8 +78,10 @@ typedef struct FrbConfig {
 #define FRB_STATIC_ASSERT(cond, msg) static_assert(cond, msg)
 #elif defined(__STDC_VERSION__) && __STDC_VERSION__ >= 201112L
 #define FRB_STATIC_ASSERT(cond, msg) _Static_assert(cond, msg)
-#else
-#define FRB_STATIC_ASSERT(cond, msg)
+#else /* C89 / C99: a negative array size is the classic compile-time check */
+#define FRB_SA_CAT2(a, b) a##b
+#define FRB_SA_CAT(a, b) FRB_SA_CAT2(a, b)
+#define FRB_STATIC_ASSERT(cond, msg) typedef char FRB_SA_CAT(frb_static_assert_line_, __LINE__)[(cond) ? 1 : -1]
 #endif
 FRB_STATIC_ASSERT(sizeof(FrbImaginary) == 16, "FrbImaginary is two doubles");
 FRB_STATIC_ASSERT(sizeof(FrbRGB) == 3, "FrbRGB is three packed bytes (the memory image of calc::RGB)");

@@ -143,6 +143,61 @@ def test_c5_frames(gpu):
     assert gpu.last_stats()["iterations"] == total
 
 
+def test_c5_frames_at_true_size(gpu):
+    """Config 5 as BASELINE.json states it: 1920x1080 (the coordinate map divides by the height, so a shrunken frame is a
+    different input at 1e12x), ten frames spread over k = 0 .. 239 through frb_render_frames — all devices, dynamic frame queue —
+    against the oracle on every 40th row: counts and final positions bit-exact (frb_render_counts), image within +-1 LSB,
+    and the animation's frames byte-identical to the same frames rendered one by one."""
+    ks = [0, 13, 57, 101, 120, 160, 199, 222, 238, 239]
+    cfgs = [configs.c5_frame(k) for k in ks]
+    h, w = cfgs[0].height, cfgs[0].width
+    out = gpu.render_frames(cfgs, gpu.FRB_RGB24, device=-1)
+    st = gpu.last_stats()
+    rows = np.arange(7, h, 40, dtype=np.uint32)
+    n = w * h * 3
+    total = 0
+    for j, cfg in enumerate(cfgs):
+        got = out[j * n:(j + 1) * n].reshape(h, w, 3)
+        ref = ob.render_rows(cfg, rows=rows)
+        iters, z = gpu.render_counts(cfg)
+        total += gpu.last_stats()["iterations"]
+        assert np.array_equal(iters[rows], ref["iters"]), f"frame {ks[j]}: counts differ"
+        assert z_equal(z[rows], ref["z"]).all(), f"frame {ks[j]}: final positions differ"
+        assert np.abs(got[rows].astype(int) - ref["rgb"].astype(int)).max() <= COLOUR_TOL, f"frame {ks[j]}"
+        single = gpu.get_image(cfg).reshape(h, w, 3)
+        assert np.array_equal(single, got), f"frame {ks[j]}: animation frame != single frame"
+    assert st["iterations"] == total and st["pixels"] == len(ks) * w * h
+
+
+def test_render_frames_leaves_room_for_other_callers(gpu):
+    """frb_render_frames locks a device per frame, not per call: a get_image issued from another thread while an animation is
+    running (the GUI's screenshot thread, src/gui.rs:325) completes long before the animation does."""
+    import threading
+    import time
+    cfgs = [configs.c5_frame(150 + (k % 40)).with_(width=960, height=540) for k in range(60)]
+    small = configs.c1().with_(width=320, height=200)
+    want = gpu.get_image(small)
+    t_anim = {}
+
+    def animate():
+        t0 = time.perf_counter()
+        gpu.render_frames(cfgs, gpu.FRB_RGB24, device=0)
+        t_anim["s"] = time.perf_counter() - t0
+
+    th = threading.Thread(target=animate)
+    th.start()
+    time.sleep(0.02)
+    lat = []
+    while th.is_alive() and len(lat) < 20:
+        t0 = time.perf_counter()
+        got = gpu.get_image(small)
+        lat.append(time.perf_counter() - t0)
+        assert np.array_equal(got, want)
+    th.join()
+    assert lat, "the animation finished before a single concurrent frame could be issued"
+    assert min(lat) < 0.5 * t_anim["s"], (min(lat), t_anim["s"])
+
+
 def test_full_size_properties_c2_variants_agree(gpu):
     """At full size, the three kernels must agree with each other bit for bit (SIMPLE is the reference order as
     written, on the GPU) and hit the exact iteration total."""
