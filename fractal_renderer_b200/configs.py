@@ -76,6 +76,31 @@ def c5(frames: int = C5_FRAMES) -> list[Config]:
     return [c5_frame(k, frames) for k in range(frames)]
 
 
+def examples_md() -> dict[str, Config]:
+    """The 14 Julia / Mandelbrot command lines of the reference's examples.md:7-29 as Configs — the only inputs the reference
+    documents.  CLI semantics (src/lib.rs:31-234): size 750x500 unless given, exposure 5, pos.re -0.6 (0 for julia), `-d` =
+    inside off, iterations from Config::new (50) unless given."""
+    j = lambda re, im, **kw: Config.cli(Algo.Julia, julia_set=Imaginary(re, im), **kw)
+    m = lambda **kw: Config.cli(Algo.Mandelbrot, **kw)
+    z = lambda s, x, y, **kw: m(scale=Imaginary(s, s), pos=Imaginary(x, y), **kw)
+    return {
+        "julia_1": j(-0.8, 0.156, iterations=2000, scale=Imaginary(0.6, 0.6), exposure=30.0, width=2000, height=1000),
+        "julia_2": j(-0.7269, 0.1889, iterations=1000, width=3000, height=1500),
+        "julia_3": j(-0.70176, 0.3842, iterations=400, exposure=25.0, width=3000, height=1500),
+        "julia_4": j(0.285, 0.01, iterations=100, exposure=10.0, width=2500, height=3000),
+        "julia_5": j(-0.2256, 0.65, iterations=500, exposure=12.0, pos=Imaginary(0.29449, -0.40460), width=2000, height=1000),
+        "julia_6": j(0.36105, 0.35977, exposure=6.0, iterations=500),
+        "mandel_classic": m(inside=False, width=3000, height=2000),
+        "mandel_golden": m(),
+        "mandel_golden_fringe": m(iterations=400),
+        "zoom_1": z(400.0, -0.7435669, 0.1314023, iterations=5000, exposure=10.0),
+        "zoom_2": z(2000.0, -0.74364990, 0.13188204, iterations=800),
+        "zoom_3": z(12000.0, -0.74364085, 0.13182733, iterations=5000, exposure=1.0),
+        "zoom_4": z(100000.0, -.743643135, .131825963, iterations=2000, inside=False, exposure=3.0),
+        "zoom_5": z(500000.0, -.7436447860, .1318252536, iterations=4000, inside=False, exposure=5.0, width=4000, height=2000),
+    }
+
+
 BY_NAME = {"C1": c1, "C2": c2, "C2b": c2b, "C3": c3, "C4": c4}
 
 # Exact loop-iteration totals (SURVEY.md §6), used as size-independent checksums at full size.

@@ -87,20 +87,124 @@ def test_frame_server_reports_render_failure_without_gpu():
         assert e.value.code == -1
 
 
+def _oracle_rgba_ok(frame, cfg, rows=None):
+    """frame (H, W, 4) against the CPU oracle: RGB within +-1 LSB (BASELINE's tolerance), alpha 255."""
+    import oracle_binding as ob
+
+    ref = ob.render_rows(cfg, rows=rows, want_iters=False, want_z=False)["rgb"]
+    got = frame if rows is None else frame[rows]
+    assert frame.shape == (cfg.height, cfg.width, 4)
+    assert (frame[..., 3] == 255).all()
+    assert np.abs(got[..., :3].astype(int) - ref.astype(int)).max() <= 1
+
+
 @pytest.mark.gpu
-def test_frame_server_renders_rgba_on_gpu(gpu):
-    cfg = configs.c1().with_(width=320, height=200)
-    want = gpu.get_image_rgba(cfg)
+def test_frame_server_scripted_session_against_the_oracle(gpu):
+    """A GUI session replayed through ViewState + FrameServer (src/gui.rs:287-341): arrow keys, scroll in and out, resize,
+    algorithm switch, more iterations — every delivered frame is checked against the ORACLE, not against the library."""
+    view = ViewState(Config.cli(Algo.Mandelbrot, width=320, height=200, iterations=120))
+    script = [
+        lambda v: None,
+        lambda v: v.apply_keys(0.25, right=True),
+        lambda v: v.apply_keys(0.25, down=True, left=True),
+        lambda v: v.apply_scroll(40.0),
+        lambda v: v.apply_scroll(120.0),
+        lambda v: v.apply_scroll(-30.0),
+        lambda v: v.set_size(417, 233),                      # ragged size
+        lambda v: setattr(v, "config", v.config.with_(iterations=700)),   # past the tile kernel's cap: deferred kernel
+        lambda v: v.apply_keys(0.1, up=True),
+        lambda v: v.set_algo(Algo.Julia),                    # resets everything to Config::new(Julia): 2000x1000, c = 0
+        lambda v: setattr(v, "config", v.config.with_(width=400, height=240, julia_set=Imaginary(-0.7269, 0.1889), iterations=300)),
+        lambda v: v.apply_scroll(80.0),
+        lambda v: v.set_size(8, 8),                          # clamped to 16x16
+    ]
     with FrameServer(device=0) as srv:
-        view = ViewState(cfg)
+        for step in script:
+            step(view)
+            srv.request(view.config)
+            frame = srv.poll(20000)
+            assert frame is not None
+            cfg = view.config
+            rows = None if cfg.height * cfg.width <= 200_000 else np.arange(3, cfg.height, 25, dtype=np.uint32)
+            _oracle_rgba_ok(frame, cfg, rows)
+        st = srv.stats()
+        assert st["frames_rendered"] == len(script) and st["coalesced"] == 0
+
+
+@pytest.mark.gpu
+def test_frame_server_fern_frames(gpu):
+    """Algo = BarnsleyFern through the server: the reference's render thread calls get_image, which draws the fern
+    (src/lib.rs:271-319) — not the all-black per-pixel arm.  The seed is entropy, so the check is structural: background =
+    secondary colour, a few per cent of the pixels darkened, alpha 255."""
+    view = ViewState()
+    view.set_algo(Algo.BarnsleyFern)
+    view.config = view.config.with_(width=400, height=200, iterations=200_000)
+    with FrameServer(device=0) as srv:
         srv.request(view.config)
-        frame = srv.poll(10000)
-        assert frame is not None and np.array_equal(frame, want)
-        view.apply_scroll(40.0)
-        srv.request(view.config)
-        frame2 = srv.poll(10000)
-        assert frame2 is not None and np.array_equal(frame2, gpu.get_image_rgba(view.config))
-        assert not np.array_equal(frame2, frame)
+        frame = srv.poll(20000)
+    assert frame is not None and frame.shape == (200, 400, 4) and (frame[..., 3] == 255).all()
+    sec = view.config.secondary_color
+    background = (frame[..., 0] == sec.r) & (frame[..., 1] == sec.g) & (frame[..., 2] == sec.b)
+    assert 0.5 < background.mean() < 0.999, background.mean()
+    rgba = gpu.get_image_rgba(view.config)
+    assert rgba.shape == frame.shape and not (rgba[..., :3] == 0).all()
+
+
+@pytest.mark.gpu
+def test_frame_server_latest_wins_under_the_gpu_renderer(gpu):
+    """Requests fired faster than frames can be rendered: every delivered frame is one of the requested states (checked against
+    the oracle), in request order, and the last delivered frame is the LAST requested state."""
+    base = configs.c2().with_(width=640, height=360, iterations=3000)
+    states = [base.with_(scale=base.scale * (1.0 + 0.01 * k)) for k in range(40)]
+    delivered = []
+    with FrameServer(device=0) as srv:
+        for k, cfg in enumerate(states):
+            srv.request(cfg)
+            f = srv.poll(0)
+            if f is not None:
+                delivered.append(f)
+        while True:
+            f = srv.poll(3000)
+            if f is None:
+                break
+            delivered.append(f)
+        st = srv.stats()
+    assert 1 <= len(delivered) <= len(states) and st["frames_rendered"] == len(delivered)
+    rows = np.arange(5, base.height, 40, dtype=np.uint32)
+    import oracle_binding as ob
+    refs = [ob.render_rows(c, rows=rows, want_iters=False, want_z=False)["rgb"] for c in states]
+    last = -1
+    for f in delivered:
+        match = [k for k in range(last + 1, len(states)) if np.abs(f[rows][..., :3].astype(int) - refs[k].astype(int)).max() <= 1]
+        assert match, "a delivered frame is none of the (later) requested states"
+        last = match[0]
+    assert np.abs(delivered[-1][rows][..., :3].astype(int) - refs[-1].astype(int)).max() <= 1, "the last frame is not the last state"
+
+
+@pytest.mark.gpu
+def test_screenshot_thread_overlaps_the_render_thread(gpu):
+    """The `S` key (src/gui.rs:319-328) renders the view at 2x on its own thread while the render thread keeps redrawing:
+    both results must be the oracle's."""
+    view = ViewState(Config.cli(Algo.Mandelbrot, width=300, height=180, iterations=400))
+    shot_cfg = view.screenshot_config()
+    result = {}
+
+    def screenshot():
+        result["img"] = gpu.get_image(shot_cfg).reshape(shot_cfg.height, shot_cfg.width, 3)
+
+    with FrameServer(device=0) as srv:
+        th = threading.Thread(target=screenshot)
+        th.start()
+        for k in range(6):
+            view.apply_scroll(20.0)
+            srv.request(view.config)
+            frame = srv.poll(20000)
+            assert frame is not None
+            _oracle_rgba_ok(frame, view.config)
+        th.join()
+    import oracle_binding as ob
+    ref = ob.render_rows(shot_cfg, want_iters=False, want_z=False)["rgb"]
+    assert np.abs(result["img"].astype(int) - ref.astype(int)).max() <= 1
 
 
 @pytest.mark.gpu
@@ -114,7 +218,7 @@ def test_frame_server_frames_are_streamed_into_pinned_memory(gpu):
             srv.request(cfg)
             frame = srv.poll(10000)
             assert frame is not None and frame.shape[:2] == (cfg.height, cfg.width)
-            assert np.array_equal(frame, gpu.get_image_rgba(cfg)), (cfg.width, cfg.height)
+            _oracle_rgba_ok(frame, cfg, np.arange(1, cfg.height, 37, dtype=np.uint32))
 
 
 def test_frame_server_acquire_hands_out_frames_without_copying():

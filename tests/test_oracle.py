@@ -102,6 +102,24 @@ def test_oracle_vs_independent_python_restatement(name):
             assert rgb == tuple(int(v) for v in r["rgb"][y, x]), (name, x, y)
 
 
+@pytest.mark.parametrize("name", sorted(configs.examples_md()))
+def test_both_restatements_agree_on_the_reference_documented_inputs(name):
+    """examples.md:7-29 holds the only inputs the reference documents (14 command lines, no expected outputs).  The C oracle and
+    the independent Python restatement must agree bit for bit on each of them AT ITS TRUE SIZE (the coordinate map depends on
+    width and height), on a grid of sample pixels."""
+    cfg = configs.examples_md()[name]
+    ys = np.linspace(0, cfg.height - 1, 6).astype(np.uint32)
+    xs = np.linspace(0, cfg.width - 1, 10).astype(int)
+    r = ob.render_rows(cfg, rows=ys)
+    for j, y in enumerate(ys):
+        for x in xs:
+            (zr, zi), n, rgb = pyref.get_recursive_pixel(cfg, int(x), int(y))
+            assert n == int(r["iters"][j, x]), (name, x, y)
+            got = r["z"][j, x]
+            assert pyref.same_bits(zr, got[0]) and pyref.same_bits(zi, got[1]), (name, x, y)
+            assert rgb == tuple(int(v) for v in r["rgb"][j, x]), (name, x, y)
+
+
 def test_rgb_new_swaps_g_and_b():
     # RGB::new(r, b, g) (calc/src/lib.rs:129-131) and color_multiply's swap (133-139): with exposure giving
     # mult = 1 the output is (P.r, P.b, P.g) of the STORED fields.
