@@ -174,7 +174,7 @@ def test_render_frames_leaves_room_for_other_callers(gpu):
     running (the GUI's screenshot thread, src/gui.rs:325) completes long before the animation does."""
     import threading
     import time
-    cfgs = [configs.c5_frame(150 + (k % 40)).with_(width=960, height=540) for k in range(60)]
+    cfgs = [configs.c5_frame(150 + (k % 40)) for k in range(100)]
     small = configs.c1().with_(width=320, height=200)
     want = gpu.get_image(small)
     t_anim = {}
@@ -195,7 +195,7 @@ def test_render_frames_leaves_room_for_other_callers(gpu):
         assert np.array_equal(got, want)
     th.join()
     assert lat, "the animation finished before a single concurrent frame could be issued"
-    assert min(lat) < 0.5 * t_anim["s"], (min(lat), t_anim["s"])
+    assert min(lat) < 0.25 * t_anim["s"], (min(lat), t_anim["s"], len(lat))
 
 
 def test_full_size_properties_c2_variants_agree(gpu):
