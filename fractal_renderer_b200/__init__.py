@@ -233,8 +233,10 @@ def render_counts(config: Config, shard: Optional[Shard] = None, device: int = 0
 
 
 def render_frames(configs: Sequence[Config], fmt: int = FRB_RGB24, device: int = -1,
-                  out: Optional[np.ndarray] = None) -> np.ndarray:
-    """Independent frames (zoom animation): frame k on device k % G.  Returns the frames back to back as bytes."""
+                  out: Optional[np.ndarray] = None, first: int = 0, stride: int = 1) -> np.ndarray:
+    """Independent frames (zoom animation), handed to the devices in order from a dynamic queue.  Returns the frames back to
+    back as bytes.  first/stride: render only frames first, first + stride, ... (one rank of a multi-process job), each into
+    its place in `out`, which addresses ALL frames."""
     n = len(configs)
     arr = (FrbConfig * max(n, 1))()
     total = 0
@@ -243,7 +245,7 @@ def render_frames(configs: Sequence[Config], fmt: int = FRB_RGB24, device: int =
         total += cfg.width * cfg.height * fmt
     if out is None:
         out = np.empty(total, np.uint8)
-    _lib.check(_lib.load().frb_render_frames(arr, n, out.ctypes.data, out.nbytes, fmt, device))
+    _lib.check(_lib.load().frb_render_frames_strided(arr, n, out.ctypes.data, out.nbytes, fmt, device, first, stride))
     return out
 
 

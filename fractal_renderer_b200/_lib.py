@@ -49,6 +49,7 @@ EXPORTS = (
     "frb_render_bands",
     "frb_render_counts",
     "frb_render_frames",
+    "frb_render_frames_strided",
     "frb_render_fern",
     "frb_fern_default_threads",
     "frb_render_device_async",
@@ -185,6 +186,9 @@ def load() -> ctypes.CDLL:
     L.frb_render_counts.argtypes = [P(FrbConfig), P(FrbShard), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     L.frb_render_frames.restype = ctypes.c_int
     L.frb_render_frames.argtypes = [P(FrbConfig), ctypes.c_uint32, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_int]
+    L.frb_render_frames_strided.restype = ctypes.c_int
+    L.frb_render_frames_strided.argtypes = [P(FrbConfig), ctypes.c_uint32, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_int,
+                                            ctypes.c_uint32, ctypes.c_uint32]
     L.frb_render_device_async.restype = ctypes.c_int
     L.frb_render_device_async.argtypes = [P(FrbConfig), P(FrbShard), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32,
                                           ctypes.c_int, ctypes.c_void_p]

@@ -26,6 +26,8 @@
 
 #include <thread>
 
+#include <sys/mman.h>
+
 namespace {
 
 using frb::RenderParams;
@@ -60,9 +62,11 @@ struct Tuning {
     int stage = 1;              // 0 = pageable destinations take the sliced copy path instead of the pinned staging pipeline
     int copy_threads = 0;       // staging pipeline: host copy threads (0 = default)
     int end_chunk = 0;          // deferred kernel: pixels per chunk in the end phase of the queue (0 = default)
+    int hugepage = 1;           // madvise(MADV_HUGEPAGE) on large pageable destinations
     int tile_direct = 1;        // tile kernel writes a pinned compact destination directly (0 = slabs + copies)
     int pool = 1;               // deferred kernel: 0 = no orbit pool (drained warps keep their lanes to the end)
     int pool_max = 31;          //                  a drained warp with at most this many live lanes donates them (<= 31)
+    int populate = 1;           // staging pipeline: first-touch the destination ahead of the copies
 };
 #ifdef FRB_TUNING
 Tuning g_tuning;
@@ -910,7 +914,21 @@ int copy_rows_out(uint8_t *host_out, size_t band_pitch, uint32_t band_rows, cons
     return FRB_OK;
 }
 
-int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot **slot_out, size_t band_pitch = 0)
+// Rows per slab of the sliced host path (equal slabs, multiples of 16 rows so that every slab starts 16-byte aligned).
+uint32_t sliced_rows_per(const RenderParams &p, int nslabs, size_t band_pitch)
+{
+    uint32_t rows_per = (p.rows + (uint32_t)nslabs - 1) / (uint32_t)nslabs;
+    rows_per = std::max(16u, (rows_per + 15u) & ~15u);
+    if (band_pitch != 0) rows_per = (rows_per + p.band_rows - 1) / p.band_rows * p.band_rows;  // slabs of whole bands
+    return rows_per;
+}
+
+void CUDART_CB raise_flag(void *flag) { *static_cast<volatile uint32_t *>(flag) = 1u; }
+
+// `ready` != nullptr: host_out is the library's pinned staging buffer (compact image) and ready[s] is raised — by a host function
+// in stream order — once slab s has arrived there (pageable destinations: a CopyJob moves it on from there).
+int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot **slot_out, size_t band_pitch = 0,
+                   uint32_t *ready = nullptr)
 {
     RenderParams &p = plan.p;
     p.out = c.b().out;
@@ -929,9 +947,7 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
     // (C2 5.58-5.78 vs 5.555 ms).
     int s = 0;
     for (uint32_t r0 = 0; r0 < p.rows; ++s) {
-        uint32_t rows_per = (p.rows + nslabs - 1) / nslabs;
-        rows_per = std::max(16u, (rows_per + 15u) & ~15u);
-        if (band_pitch != 0) rows_per = (rows_per + p.band_rows - 1) / p.band_rows * p.band_rows;  // slabs of whole bands
+        const uint32_t rows_per = sliced_rows_per(p, nslabs, band_pitch);
         cudaStream_t ks = c.aux[s & 1];
         cudaStream_t cs = ks;
         if (s < 2) CU(cudaStreamWaitEvent(c.aux[s & 1], c.ev_fork, 0));
@@ -957,6 +973,7 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
             slot.launches += 2;
         }
         if (int rc = copy_rows_out(host_out, band_pitch, p.band_rows, sh.out, r0, r1, (size_t)p.width * p.format, cs)) return rc;
+        if (ready != nullptr) CU(cudaLaunchHostFunc(cs, raise_flag, ready + s));
         r0 = r1;
     }
     for (int i = 0; i < 2; ++i) {
@@ -1086,6 +1103,43 @@ public:
 };
 StagePool g_stage;
 
+// Asks the kernel to back a large destination with huge pages (THP in "madvise" mode, the default of most distributions): a fresh
+// 50 MB Vec is 12 800 first-touch faults of 4 KB — or 25 of 2 MB.  A hint about memory the caller owns: it changes how the pages
+// behind it are allocated, never their contents.  Failure (not anonymous memory, THP off) is ignored.
+void advise_huge_pages(uint8_t *p, size_t bytes)
+{
+    if (!tuning().hugepage || bytes < ((size_t)4 << 20)) return;
+    const uintptr_t page = 4096;
+    const uintptr_t a = (reinterpret_cast<uintptr_t>(p) + page - 1) & ~(page - 1);
+    const uintptr_t e = (reinterpret_cast<uintptr_t>(p) + bytes) & ~(page - 1);
+    if (e > a) madvise(reinterpret_cast<void *>(a), e - a, MADV_HUGEPAGE);
+}
+
+// First touch of destination pages without changing what they hold.  MADV_POPULATE_WRITE (Linux 5.14) faults a whole range in
+// one system call; older kernels get one atomic OR-with-zero per page, which cannot lose a byte another thread is copying into
+// the same page.  Every page touched holds at least one byte of the caller's buffer.
+#ifndef MADV_POPULATE_WRITE
+#define MADV_POPULATE_WRITE 23
+#endif
+std::atomic<int> g_populate_by_madvise{1};
+
+void populate_range(uint8_t *lo, uint8_t *hi)
+{
+    if (hi <= lo) return;
+    const uintptr_t page = 4096;
+    const uintptr_t a = reinterpret_cast<uintptr_t>(lo) & ~(page - 1);
+    const uintptr_t e = (reinterpret_cast<uintptr_t>(hi) + page - 1) & ~(page - 1);
+    if (g_populate_by_madvise.load(std::memory_order_relaxed)) {
+        if (madvise(reinterpret_cast<void *>(a), e - a, MADV_POPULATE_WRITE) == 0) return;
+        if (errno == EINVAL) g_populate_by_madvise.store(0, std::memory_order_relaxed);  // kernel without it
+        else if (errno != EAGAIN && errno != EINTR) return;  // not ours to populate (file mapping without room, ...): the copy will fault it
+    }
+    for (uintptr_t q = a; q < e; q += page) {
+        uint8_t *b = reinterpret_cast<uint8_t *>(std::max(q, reinterpret_cast<uintptr_t>(lo)));
+        __atomic_fetch_or(b, (uint8_t)0, __ATOMIC_RELAXED);
+    }
+}
+
 // One frame's copy work: slabs claimed through an atomic counter by the helper threads and, once its stream has drained, by the
 // rendering thread itself.
 struct CopyJob {
@@ -1099,6 +1153,32 @@ struct CopyJob {
     std::atomic<uint32_t> next{0};
     std::atomic<bool> abort{false};
     std::atomic<int> running{0};
+    // first touch ahead of the copies: pieces of the destination (512 KB of a compact image, one band of a framed one) are
+    // populated by whichever thread is free while the first slabs are still being iterated
+    uint32_t npieces = 0;
+    std::atomic<uint32_t> next_piece{0};
+    static constexpr size_t kPieceBytes = (size_t)512 << 10;
+
+    void plan_populate()
+    {
+        if (!tuning().populate || !dst || rows == 0) return;
+        const size_t bytes = (size_t)rows * row_bytes;
+        npieces = framed ? (rows + band_rows - 1) / band_rows : (uint32_t)((bytes + kPieceBytes - 1) / kPieceBytes);
+    }
+    void populate_piece(uint32_t i) const
+    {
+        uint8_t *lo, *hi;
+        if (framed) {
+            const uint32_t r0 = i * band_rows, r1 = std::min(rows, r0 + band_rows);
+            lo = dst + ((size_t)i * shard_count + shard_index) * band_rows * row_bytes;
+            hi = lo + (size_t)(r1 - r0) * row_bytes;
+        } else {
+            const size_t bytes = (size_t)rows * row_bytes;
+            lo = dst + (size_t)i * kPieceBytes;
+            hi = dst + std::min(bytes, (size_t)(i + 1) * kPieceBytes);
+        }
+        populate_range(lo, hi);
+    }
 
     void copy_slab(uint32_t s) const
     {
@@ -1118,6 +1198,11 @@ struct CopyJob {
     // Claims slabs until none is left (or the frame was abandoned).  Every participant was counted in `running` beforehand.
     void run()
     {
+        for (;;) {
+            const uint32_t i = next_piece.load(std::memory_order_relaxed) < npieces ? next_piece.fetch_add(1, std::memory_order_relaxed) : npieces;
+            if (i >= npieces || abort.load(std::memory_order_relaxed)) break;
+            populate_piece(i);
+        }
         for (;;) {
             const uint32_t s = next.fetch_add(1, std::memory_order_relaxed);
             if (s >= nslabs) break;
@@ -1268,6 +1353,8 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
         job->shard_count = sh.count;
         const int helpers = g_copy.helpers();
         job->running.store(helpers + 1);
+        advise_huge_pages(framed ? host_out : dst0, framed ? row_bytes * cfg.height : plan.out_bytes);
+        job->plan_populate();
         int rc = enqueue_streamed(*c, plan, sb->p, c->stream, &slot, sb->done);
         if (!rc) rc = finish_enqueue(*c, *slot, c->stream);
         if (rc) {
@@ -1329,7 +1416,43 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
         // 32 Mpx, 8 up to 64 Mpx, 16 beyond (C2 5.24 ms with 4; C4 213.5 / 211.4 / 210.5 ms with 4 / 8 / 16)
         int nslabs = plan.npix >= (64u << 20) ? 16 : (plan.npix >= (32u << 20) ? 8 : 4);
         if (tuning().slabs > 0) nslabs = std::min(16, tuning().slabs);
-        if (int rc = enqueue_sliced(*c, plan, dst0, nslabs, &slot, band_pitch)) return rc;
+        // A pageable destination gets its slabs through pinned staging and the copy threads as well (the tile kernel's frames,
+        // the dense kernels'): device -> staging at DMA speed, staging -> destination by several threads, first touch included.
+        StageBuf *sb2 = nullptr;
+        if (tuning().stage && plan.out_bytes <= kMaxStageBytes && device_alias_of_host(host_out) == nullptr) sb2 = g_stage.acquire(plan.out_bytes);
+        if (sb2) {
+            if (tile && nslabs < 8) nslabs = 8;  // short frames: smaller slabs start the host copies earlier
+            const uint32_t rows_per = sliced_rows_per(plan.p, nslabs, 0);
+            const uint32_t nsl = (plan.p.rows + rows_per - 1) / rows_per;
+            memset(sb2->done, 0, (size_t)nsl * sizeof(uint32_t));
+            auto job = std::make_shared<CopyJob>();
+            job->stage = sb2->p;
+            job->dst = host_out;
+            job->row_bytes = row_bytes;
+            job->rows = plan.p.rows;
+            job->slab_rows = rows_per;
+            job->nslabs = nsl;
+            job->done = sb2->done;
+            job->framed = framed;
+            job->band_rows = plan.p.band_rows;
+            job->shard_index = sh.index;
+            job->shard_count = sh.count;
+            const int helpers = g_copy.helpers();
+            job->running.store(helpers + 1);
+            advise_huge_pages(framed ? host_out : dst0, framed ? row_bytes * cfg.height : plan.out_bytes);
+            job->plan_populate();
+            int rc = enqueue_sliced(*c, plan, sb2->p, nslabs, &slot, 0, sb2->done);
+            if (rc) {
+                g_stage.release(sb2);
+                return rc;
+            }
+            g_copy.post(job, helpers);
+            job->run();  // the flags are raised in stream order: the rendering thread copies along
+            job->wait_idle();
+            g_stage.release(sb2);
+        } else if (int rc = enqueue_sliced(*c, plan, dst0, nslabs, &slot, band_pitch)) {
+            return rc;
+        }
     } else {
         if (int rc = enqueue(*c, plan, c->b().out, c->stream, &slot)) return rc;
         if (plan.npix > 0) {
@@ -1649,9 +1772,10 @@ int frb_set_tuning(const char *name, int64_t value)
         {"stream", &Tuning::stream},         {"stream_gen_polls", &Tuning::stream_gen_polls},
         {"stream_rows", &Tuning::stream_rows}, {"stream_ctas", &Tuning::stream_ctas},
         {"slabs", &Tuning::slabs},           {"no_slab", &Tuning::no_slab},
-        {"stage", &Tuning::stage},           {"copy_threads", &Tuning::copy_threads},
+        {"stage", &Tuning::stage},           {"copy_threads", &Tuning::copy_threads}, {"populate", &Tuning::populate},
         {"end_chunk", &Tuning::end_chunk},   {"pool", &Tuning::pool},
         {"pool_max", &Tuning::pool_max},     {"tile_direct", &Tuning::tile_direct},
+        {"hugepage", &Tuning::hugepage},
     };
     std::lock_guard<std::mutex> lk(g_mu);
     if (strcmp(name, "reset") == 0) {
@@ -1924,7 +2048,15 @@ int frb_render(const FrbConfig *cfg, uint8_t *out, size_t out_len, uint32_t form
 
 int frb_render_frames(const FrbConfig *cfgs, uint32_t n, uint8_t *out, size_t out_len, uint32_t format, int device)
 {
+    return frb_render_frames_strided(cfgs, n, out, out_len, format, device, 0u, 1u);
+}
+
+int frb_render_frames_strided(const FrbConfig *cfgs, uint32_t n, uint8_t *out, size_t out_len, uint32_t format, int device,
+                              uint32_t first, uint32_t stride)
+{
     if (!cfgs && n) return fail(FRB_ERR_INVALID, "null configs");
+    if (stride == 0u) return fail(FRB_ERR_INVALID, "zero frame stride");
+    const uint32_t mine = first < n ? (n - first + stride - 1u) / stride : 0u;  // frames first, first + stride, ... below n
     if (format != FRB_RGB24 && format != FRB_RGBA32) return fail(FRB_ERR_INVALID, "unknown pixel format %u", format);
     size_t need = 0;
     for (uint32_t k = 0; k < n; ++k) need += (size_t)cfgs[k].width * cfgs[k].height * format;
@@ -1996,8 +2128,9 @@ int frb_render_frames(const FrbConfig *cfgs, uint32_t n, uint8_t *out, size_t ou
         };
         for (;;) {
             while (npending < 2 && !failed.load(std::memory_order_relaxed)) {
-                const uint32_t k = next.fetch_add(1, std::memory_order_relaxed);
-                if (k >= n) break;
+                const uint32_t j = next.fetch_add(1, std::memory_order_relaxed);
+                if (j >= mine) break;
+                const uint32_t k = first + j * stride;
                 std::lock_guard<std::mutex> lk(c.mu);
                 const int alt = (int)(nth++ & 1u);
                 c.cur_set = alt;

@@ -222,6 +222,12 @@ int frb_render_counts(const FrbConfig *cfg, const FrbShard *shard, uint32_t *ite
  * all to `device`; out holds the frames back to back, each width_k*height_k*format bytes. */
 int frb_render_frames(const FrbConfig *cfgs, uint32_t n, uint8_t *out, size_t out_len, uint32_t format,
                       int device);
+/* The same for one process of a one-process-per-GPU job: renders only the frames first, first + stride, first + 2 stride, ...
+ * (rank and world size) — each into ITS place in `out`, which addresses all n frames (a frb_shared_frame, say), so the animation
+ * is complete when every process has returned.  Frames go to the devices in order from a dynamic queue, one host thread per
+ * device, two frames in flight on each. */
+int frb_render_frames_strided(const FrbConfig *cfgs, uint32_t n, uint8_t *out, size_t out_len, uint32_t format,
+                              int device, uint32_t first, uint32_t stride);
 
 /* ---- Barnsley fern: the other arm of get_image (src/lib.rs:271-319, 417-463) --------------------------------- */
 
