@@ -67,6 +67,7 @@ struct Tuning {
     int pool = 1;               // deferred kernel: 0 = no orbit pool (drained warps keep their lanes to the end)
     int pool_max = 31;          //                  a drained warp with at most this many live lanes donates them (<= 31)
     int populate = 1;           // staging pipeline: first-touch the destination ahead of the copies
+    int tile_smem_kb = 0;       // tile kernel: unused dynamic shared memory per CTA, to cap the CTAs resident per SM (experiments)
 };
 #ifdef FRB_TUNING
 Tuning g_tuning;
@@ -128,6 +129,9 @@ struct DeviceCtx {
     // tile-kernel feedback: the scene (tile_key_of) whose last tile-kernel frame ran with poor lane utilisation, and for how
     // many more frames the library keeps the lane-refill kernel for it before trying the tile kernel again
     std::vector<const void *> loaded_kernels;  // preload_kernel(): kernels whose code is known to be on the device
+    // callers blocked on `mu` in a blocking render: frb_render_frames gives way to them between two frames (a std::mutex is
+    // not fair: a thread that unlocks and locks again at once can starve a waiter for the whole animation)
+    std::atomic<int> waiting{0};
     std::atomic<uint64_t> tile_bad_key{0};
     std::atomic<uint32_t> tile_bad_frames{0};
     cudaStream_t aux[2] = {nullptr, nullptr};  // slab streams of the host-output path
@@ -485,6 +489,9 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     p.height = cfg.height;
     p.rows = shard_rows(cfg.height, sh);
     p.band_rows = shard_band_rows(cfg.height, sh);
+    p.band_shift = 32u;
+    for (uint32_t k = 0; k < 32u; ++k)
+        if (p.band_rows == (1u << k)) p.band_shift = k;
     p.shard_index = sh.index;
     p.shard_count = sh.count;
     p.iterations = cfg.iterations;
@@ -539,10 +546,10 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     // (DEFER6 -> DENSE6 -> STREAM7); FrbStats.kernel_variant reports what actually ran.
     // short orbits, image wanted: the lock-step tile kernel (per-pixel costs of the refill kernels outweigh their lane
     // utilisation there).  It has no raw-result output (format 0 falls through), and its grid puts 8 rows on blockIdx.y.
-    const uint32_t tile_max = (uint32_t)std::max(0, tuning().tile_max);
+    const uint32_t tile_max = (uint32_t)std::min(65535, std::max(0, tuning().tile_max));  // its statistics are 32-bit sums per CTA
     const bool tile_fits = (p.rows + 7u) / 8u <= 65535u;
     plan->fern = cfg.algo == FRB_ALGO_BARNSLEY_FERN;  // get_recursive_pixel returns BLACK for it: nothing to iterate
-    if (v == FRB_KERNEL_TILE && (format == 0 || plan->fern || !tile_fits)) v = FRB_KERNEL_AUTO;
+    if (v == FRB_KERNEL_TILE && (format == 0 || plan->fern || !tile_fits || cfg.iterations > 65535u)) v = FRB_KERNEL_AUTO;
     plan->tile_key = 0;
     if (v == FRB_KERNEL_AUTO && format != 0 && cfg.iterations <= tile_max && !plan->fern && tile_fits) {
         // The cap says nothing about how orbit lengths are mixed inside a tile, and lock-step warps pay for the longest lane
@@ -640,8 +647,9 @@ int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaSt
         // iterates AND shades: the caller skips the shade kernel
         dim3 grid((p.width + frb::kTileW - 1) / frb::kTileW, (p.rows + frb::kTileH - 1) / frb::kTileH);
         if (grid.y > 65535u) return fail(FRB_ERR_TOO_LARGE, "tile kernel: %u rows exceed the grid's y extent", p.rows);
-        if (plan.tile_form == 6) frb::frb_iterate_tile_kernel<6><<<grid, frb::kTileW * frb::kTileH, 0, st>>>(p);
-        else frb::frb_iterate_tile_kernel<7><<<grid, frb::kTileW * frb::kTileH, 0, st>>>(p);
+        const size_t dyn = (size_t)std::min(44, std::max(0, tuning().tile_smem_kb)) << 10;
+        if (plan.tile_form == 6) frb::frb_iterate_tile_kernel<6><<<grid, frb::kTileW * frb::kTileH, dyn, st>>>(p);
+        else frb::frb_iterate_tile_kernel<7><<<grid, frb::kTileW * frb::kTileH, dyn, st>>>(p);
         return FRB_OK;
     }
     const uint32_t warps_per_block = frb::kIterateThreads / 32;
@@ -1299,7 +1307,9 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
     const double t0 = now_ms();
     DeviceCtx *c = get_ctx(dev);
     if (!c) return tl_code;
+    c->waiting.fetch_add(1, std::memory_order_relaxed);
     std::lock_guard<std::mutex> lk(c->mu);
+    c->waiting.fetch_sub(1, std::memory_order_relaxed);
     CU(cudaSetDevice(dev));
     Plan plan;
     if (int rc = make_plan(*c, cfg, sh, format, &plan)) return rc;
@@ -1778,7 +1788,7 @@ int frb_set_tuning(const char *name, int64_t value)
         {"stream", &Tuning::stream},         {"stream_gen_polls", &Tuning::stream_gen_polls},
         {"stream_rows", &Tuning::stream_rows}, {"stream_ctas", &Tuning::stream_ctas},
         {"slabs", &Tuning::slabs},           {"no_slab", &Tuning::no_slab},
-        {"stage", &Tuning::stage},           {"copy_threads", &Tuning::copy_threads}, {"populate", &Tuning::populate},
+        {"stage", &Tuning::stage},           {"copy_threads", &Tuning::copy_threads}, {"populate", &Tuning::populate}, {"tile_smem_kb", &Tuning::tile_smem_kb},
         {"end_chunk", &Tuning::end_chunk},   {"pool", &Tuning::pool},
         {"pool_max", &Tuning::pool_max},     {"tile_direct", &Tuning::tile_direct},
         {"hugepage", &Tuning::hugepage},
@@ -2137,6 +2147,9 @@ int frb_render_frames_strided(const FrbConfig *cfgs, uint32_t n, uint8_t *out, s
                 const uint32_t j = next.fetch_add(1, std::memory_order_relaxed);
                 if (j >= mine) break;
                 const uint32_t k = first + j * stride;
+                // a blocking render from another thread goes first (bounded: it holds the device for one frame of its own)
+                for (int spin = 0; c.waiting.load(std::memory_order_relaxed) > 0 && spin < 4000; ++spin)
+                    std::this_thread::sleep_for(std::chrono::microseconds(50));
                 std::lock_guard<std::mutex> lk(c.mu);
                 const int alt = (int)(nth++ & 1u);
                 c.cur_set = alt;

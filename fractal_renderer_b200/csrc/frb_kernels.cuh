@@ -64,6 +64,8 @@ struct RenderParams {
     // (q_cpr2 per row).  total_chunks counts both.  q_pool_max: a drained warp with at most this many live lanes hands them to
     // the CTA's orbit pool and leaves (0 = no pool).
     uint32_t q_row0, q_rows_big, q_nbig, q_cpr2, q_chunk2, q_pool_max;
+    uint32_t band_shift;    // log2(band_rows) when band_rows is a power of two (the default bands of 16 rows), else 32
+    uint32_t pad_band;
     // Output addressing of K2 / K2s.  out_band_q == 0: `out` is this launch's own compact image.  Otherwise `out` is where the
     // shard's band 0 starts inside a WHOLE frame shared with other devices' shards (frb_render, device = -1): compact byte offset
     // o of the shard maps to o + (o / band_bytes) * out_band_gap, band_bytes = 16 * out_band_q (one band of kDefaultBandRows rows),
@@ -107,6 +109,11 @@ __host__ __device__ inline void offset_out(RenderParams &sub, const RenderParams
 // local (compact) row of a shard -> image row; see FrbShard in include/frb.h
 __device__ __forceinline__ uint32_t local_row_to_y(const RenderParams &p, uint32_t lr)
 {
+    if (p.shard_count == 1u) return lr;  // one shard: its rows are the image's
+    if (p.band_shift < 32u) {
+        const uint32_t band = lr >> p.band_shift;
+        return ((band * p.shard_count + p.shard_index) << p.band_shift) + (lr & (p.band_rows - 1u));
+    }
     const uint32_t band = lr / p.band_rows;
     const uint32_t r = lr - band * p.band_rows;
     return (band * p.shard_count + p.shard_index) * p.band_rows + r;
@@ -446,12 +453,14 @@ __device__ __forceinline__ void load_log2_table(double2 *dst)  // dst: 128 entri
     for (unsigned i = threadIdx.x; i < 128u; i += blockDim.x) dst[i] = g_log2_table[i];
 }
 
-// x positive, normal, finite.
+// x positive, normal, finite.  GLOBAL_TABLE: `tbl` is g_log2_table itself, read through the read-only cache (the tile kernel);
+// otherwise a copy in shared memory.
+template <bool GLOBAL_TABLE = false>
 __device__ __forceinline__ double shade_log2(double x, const double2 *tbl)
 {
     const uint32_t hi = (uint32_t)__double2hiint(x);
     const double m = __hiloint2double((int)((hi & 0x000fffffu) | 0x3ff00000u), __double2loint(x));
-    const double2 t = tbl[(hi >> 13) & 127u];
+    const double2 t = GLOBAL_TABLE ? __ldg(tbl + ((hi >> 13) & 127u)) : tbl[(hi >> 13) & 127u];
     const double r = fma(m, t.x, -1.0);
     // biased exponent -> double without a conversion instruction: the bits of 2^52 + E, minus (2^52 + 1023)
     const double e = __dsub_rn(__hiloint2double(0x43300000, (int)(hi >> 20)), 4503599627371519.0);
@@ -465,6 +474,7 @@ __device__ __forceinline__ double shade_log2(double x, const double2 *tbl)
 
 // get_recursive_pixel after recursive() (calc/src/lib.rs:214-234).  Returns r | g<<8 | b<<16.  `lg` = the log2 table in
 // shared memory.
+template <bool GLOBAL_TABLE = false>
 __device__ __forceinline__ uint32_t shade_pixel(const RenderParams &p, uint32_t count, double2 z, const double2 *lg)
 {
     if (p.algo == kAlgoFern) return 0u;  // `_ => return RGB::BLACK`
@@ -475,8 +485,8 @@ __device__ __forceinline__ uint32_t shade_pixel(const RenderParams &p, uint32_t 
         if (p.smooth) {
             // 2 <= dist < inf  (high words 0x40000000 .. 0x7fefffff): both logarithms take the table path
             if (fast && (uint32_t)__double2hiint(dist) - 0x40000000u < 0x3ff00000u) {
-                const double log_zn = __dmul_rn(shade_log2(dist, lg), 0.25);  // log2(sqrt(dist)) / 2
-                it = __dadd_rn(it, __dsub_rn(1.0, shade_log2(log_zn, lg)));
+                const double log_zn = __dmul_rn(shade_log2<GLOBAL_TABLE>(dist, lg), 0.25);  // log2(sqrt(dist)) / 2
+                it = __dadd_rn(it, __dsub_rn(1.0, shade_log2<GLOBAL_TABLE>(log_zn, lg)));
             } else {
                 const double log_zn = __ddiv_rn(log2(__dsqrt_rn(dist)), 2.0);
                 const double nu = log2(log_zn);

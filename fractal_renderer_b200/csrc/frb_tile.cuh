@@ -7,7 +7,8 @@
 // a small iteration cap the lock-step alternative cannot lose much: a tile costs at most cap x 16 cycles, and measured tile
 // utilisation is high exactly where orbits are short (C1, 8x4 tiles: 0.93 — SURVEY Appendix C).  So frames whose cap is at
 // most kTileMaxIterations (frb_api.cu) take this kernel: per iteration the same 6 (or, where FORM 6 is not provably exact,
-// 7) FP64 instructions as everywhere else plus VIMNMX / ISETP / BRA, no queue, no records, no second kernel.
+// 7) FP64 instructions as everywhere else plus the filter of a PAIR of iterations (VIMNMX, VIMNMX3, ISETP, BRA), no queue, no
+// records, no second kernel.
 // Same arithmetic, same exact test (calc/src/lib.rs:249-254 on the carried squares), so counts and final positions are the
 // ones every other kernel produces; the raw-result path (frb_render_counts) keeps using those.
 #pragma once
@@ -21,10 +22,8 @@ __global__ void __launch_bounds__(kTileW * kTileH)
 frb_iterate_tile_kernel(const __grid_constant__ RenderParams p)
 {
     __shared__ __align__(16) uint8_t stage[kTileH][kTileW * 4];
-    __shared__ double2 lg[128];
-    __shared__ unsigned long long s_useful[kTileH];
+    __shared__ uint32_t s_useful[kTileH];
     __shared__ uint32_t s_longest[kTileH];
-    load_log2_table(lg);  // needed by shade_pixel only: the barrier that publishes it comes after the loop
     const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     const uint32_t tx = (warp & 3u) * 8u + (lane & 7u), ty = (warp >> 2) * 4u + (lane >> 3);
     const uint32_t x = blockIdx.x * kTileW + tx;
@@ -42,56 +41,132 @@ frb_iterate_tile_kernel(const __grid_constant__ RenderParams p)
         const double S = p.limit_sq;
         const uint32_t filter_hi = p.filter_hi;
         const uint32_t iterations = p.iterations;
+        const uint32_t n4 = iterations & ~3u;
         count = iterations;
-        // recursive (calc/src/lib.rs:245-257): (next, i) on escape, (previous, iterations) otherwise.  Four iterations per
-        // loop trip; per iteration the 6 (7) FP64 instructions, VIMNMX + ISETP + BRA for the filter, and nothing else: the
-        // exact test and the count live behind the (rarely taken) filter branch.
+        // recursive (calc/src/lib.rs:245-257): (next, i) on escape, (previous, iterations) otherwise.
+        // The steady state is a loop of four iterations with ONE filter test per pair: max(hi(re^2), hi(im^2)) over both
+        // positions of the pair on the integer pipe (VIMNMX, VIMNMX3), ISETP, BRA — 8.75 issue slots an iteration for 6 on
+        // the FP64 pipe, which is what bounds the loop.  A pair computed past an escape is harmless: squares grow to inf or
+        // NaN, whose high words also fire the filter, and only the positions up to the first exact escape are used.  A lane
+        // whose filter fires LEAVES the loop and only outside it runs the exact tests, the count, and — when the filter fired
+        // early (S/2 <= max(re^2, im^2) but re^2 + im^2 <= S) — the exact steps up to the next multiple of four before it goes
+        // back in.  Leaving (instead of an `if` inside the body) keeps the convergence barrier (BSSY/BSYNC: two issue slots
+        // an iteration in the first version of this kernel) out of the loop; the price is that a lane with an early hit
+        // waits outside until the others leave as well, which costs nothing where it matters (limit^2 >= 8: the step after
+        // an early hit escapes; and escaped lanes idle to the end of the tile anyway).
         uint32_t i = 0;
-        // The exact test sits in a PTX loop that never repeats (i < iterations <= 2^32 - 1): a back edge is the one thing
-        // ptxas will not if-convert, so DADD + DSETP run only behind the filter branch instead of on every iteration.
-#define FRB_TILE_STEP(K)                                                                              \
-    stream_core<FORM>(o);                                                                             \
-    if (stream_filter(o, filter_hi)) {                                                                \
-        uint32_t esc;                                                                                 \
-        asm volatile("{\n\t.reg .pred q, r;\n\t.reg .f64 s;\n"                                         \
-                     "FRB_TILE_%=:\n\t"                                                               \
-                     "add.rn.f64 s, %1, %2;\n\t"                                                      \
-                     "setp.gt.f64 q, s, %3;\n\t"                                                      \
-                     "selp.u32 %0, 1, 0, q;\n\t"                                                      \
-                     "setp.eq.u32 r, %4, 0xffffffff;\n\t"                                             \
-                     "@r bra FRB_TILE_%=;\n\t}"                                                       \
-                     : "=r"(esc)                                                                      \
-                     : "d"(o.a), "d"(o.b), "d"(S), "r"(i));                                           \
-        if (esc) {                                                                                    \
-            count = i + (K);                                                                          \
-            goto escaped;                                                                             \
-        }                                                                                             \
-    }
-        for (const uint32_t n4 = iterations & ~3u; i < n4; i += 4) {
-            FRB_TILE_STEP(0)
-            FRB_TILE_STEP(1)
-            FRB_TILE_STEP(2)
-            FRB_TILE_STEP(3)
+        for (;;) {
+            Orbit pre = o;
+            uint32_t k;
+            // Written in PTX: from C++ the compiler recomputed squares on both sides of the filter branch and carried the
+            // exit index through the loop (26 FP64 and 12 other instructions per four iterations instead of 24 and 11).
+            // Exits: k = 4 with i == n4 (no hit), or k = 0 / 2 = first iteration of the pair that fired, `pre` = the position
+            // after that iteration and `o` = the position after the second one.
+#define FRB_STEP6(X, Y, A, B, NX, NY, NA, NB)                \
+    "sub.rn.f64 s, " A ", " B ";\n\t"                        \
+    "mul.rn.f64 t, " X ", " Y ";\n\t"                        \
+    "add.rn.f64 " NX ", s, %10;\n\t"                         \
+    "fma.rn.f64 " NY ", t, 0d4000000000000000, %11;\n\t"     \
+    "mul.rn.f64 " NA ", " NX ", " NX ";\n\t"                 \
+    "mul.rn.f64 " NB ", " NY ", " NY ";\n\t"
+#define FRB_STEP7(X, Y, A, B, NX, NY, NA, NB)                \
+    "sub.rn.f64 s, " A ", " B ";\n\t"                        \
+    "add.rn.f64 t, " X ", " X ";\n\t"                        \
+    "mul.rn.f64 t, t, " Y ";\n\t"                            \
+    "add.rn.f64 " NX ", s, %10;\n\t"                         \
+    "add.rn.f64 " NY ", t, %11;\n\t"                         \
+    "mul.rn.f64 " NA ", " NX ", " NX ";\n\t"                 \
+    "mul.rn.f64 " NB ", " NY ", " NY ";\n\t"
+#define FRB_PAIR_FILTER(A1, B1, A2, B2, TARGET)              \
+    "mov.b64 {lo, h1}, " A1 ";\n\t"                          \
+    "mov.b64 {lo, h2}, " B1 ";\n\t"                          \
+    "mov.b64 {lo, h3}, " A2 ";\n\t"                          \
+    "mov.b64 {lo, h4}, " B2 ";\n\t"                          \
+    "max.u32 h1, h1, h2;\n\t"                                \
+    "max.u32 h3, h3, h4;\n\t"                                \
+    "max.u32 h1, h1, h3;\n\t"                                \
+    "setp.ge.u32 q, h1, %13;\n\t"                            \
+    "@q bra " TARGET ";\n\t"
+#define FRB_TILE_LOOP(STEP)                                                                                                 \
+    asm volatile("{\n\t"                                                                                                    \
+                 ".reg .f64 s, t, x1, y1, a1, b1, x2, y2, a2, b2, x3, y3, a3, b3;\n\t"                                      \
+                 ".reg .u32 lo, h1, h2, h3, h4;\n\t"                                                                        \
+                 ".reg .pred q;\n\t"                                                                                        \
+                 "mov.u32 %9, 4;\n\t"                                                                                       \
+                 "setp.ge.u32 q, %8, %12;\n\t"                                                                              \
+                 "@q bra FRB_DONE;\n"                                                                                       \
+                 "FRB_LOOP:\n\t"                                                                                            \
+                 STEP("%0", "%1", "%2", "%3", "x1", "y1", "a1", "b1")                                                       \
+                 STEP("x1", "y1", "a1", "b1", "x2", "y2", "a2", "b2")                                                       \
+                 FRB_PAIR_FILTER("a1", "b1", "a2", "b2", "FRB_HIT0")                                                        \
+                 STEP("x2", "y2", "a2", "b2", "x3", "y3", "a3", "b3")                                                       \
+                 STEP("x3", "y3", "a3", "b3", "%0", "%1", "%2", "%3")                                                       \
+                 FRB_PAIR_FILTER("a3", "b3", "%2", "%3", "FRB_HIT2")                                                        \
+                 "add.u32 %8, %8, 4;\n\t"                                                                                   \
+                 "setp.lt.u32 q, %8, %12;\n\t"                                                                              \
+                 "@q bra FRB_LOOP;\n\t"                                                                                     \
+                 "bra FRB_DONE;\n"                                                                                          \
+                 "FRB_HIT0:\n\t"                                                                                            \
+                 "mov.f64 %4, x1;\n\tmov.f64 %5, y1;\n\tmov.f64 %6, a1;\n\tmov.f64 %7, b1;\n\t"                             \
+                 "mov.f64 %0, x2;\n\tmov.f64 %1, y2;\n\tmov.f64 %2, a2;\n\tmov.f64 %3, b2;\n\t"                             \
+                 "mov.u32 %9, 0;\n\t"                                                                                       \
+                 "bra FRB_DONE;\n"                                                                                          \
+                 "FRB_HIT2:\n\t"                                                                                            \
+                 "mov.f64 %4, x3;\n\tmov.f64 %5, y3;\n\tmov.f64 %6, a3;\n\tmov.f64 %7, b3;\n\t"                             \
+                 "mov.u32 %9, 2;\n"                                                                                         \
+                 "FRB_DONE:\n\t"                                                                                            \
+                 "}"                                                                                                        \
+                 : "+d"(o.x), "+d"(o.y), "+d"(o.a), "+d"(o.b), "+d"(pre.x), "+d"(pre.y), "+d"(pre.a), "+d"(pre.b), "+r"(i), \
+                   "=r"(k)                                                                                                  \
+                 : "d"(o.cr), "d"(o.ci), "r"(n4), "r"(filter_hi))
+            if (FORM == 6) FRB_TILE_LOOP(FRB_STEP6);
+            else FRB_TILE_LOOP(FRB_STEP7);
+#undef FRB_TILE_LOOP
+#undef FRB_PAIR_FILTER
+#undef FRB_STEP7
+#undef FRB_STEP6
+            if (k == 4u) break;  // i == n4: fewer than four iterations left
+            i += k;              // index of the first iteration of the pair
+            if (stream_escaped(pre, S)) {
+                count = i;
+                o.x = pre.x, o.y = pre.y;
+                goto escaped;
+            }
+            ++i;
+            if (stream_escaped(o, S)) {
+                count = i;
+                goto escaped;
+            }
+            for (++i; (i & 3u) != 0u; ++i) {  // the pair began below n4, so the next multiple of four is at most n4
+                stream_core<FORM>(o);
+                if (stream_escaped(o, S)) {
+                    count = i;
+                    goto escaped;
+                }
+            }
         }
         for (; i < iterations; ++i) {
-            FRB_TILE_STEP(0)
+            stream_core<FORM>(o);
+            if (stream_escaped(o, S)) {
+                count = i;
+                break;
+            }
         }
-#undef FRB_TILE_STEP
     escaped:;
     }
-    __syncthreads();
-    const uint32_t c = valid ? shade_pixel(p, count, make_double2(o.x, o.y), lg) : 0u;
+    // colour straight from the registers; the log2 table (2 KB) is read through the read-only cache: no copy to shared memory and
+    // no barrier between a warp's last iteration and its shading
+    const uint32_t c = valid ? shade_pixel<true>(p, count, make_double2(o.x, o.y), g_log2_table) : 0u;
 
     // statistics: loop-body executions (i + 1 | iterations) and the lane slots the lock-step warps spent (32 x the longest orbit),
     // summed over the CTA first: two same-address atomics per WARP (65 000 warps on C1) serialise in the L2 for longer than
-    // the frame takes to iterate
+    // the frame takes to iterate.  The kernel only runs caps below 2^16 (frb_api.cu: make_plan), so a warp's sum fits a word.
     {
         const uint32_t useful = (valid && p.iterations != 0u) ? min(count, p.iterations - 1u) + 1u : 0u;
         const uint32_t longest = __reduce_max_sync(0xffffffffu, useful);
-        const uint32_t lo = __reduce_add_sync(0xffffffffu, useful & 0xffffu);  // two halves: 32 x 2^32 does not fit a word
-        const uint32_t hi = __reduce_add_sync(0xffffffffu, useful >> 16);
+        const uint32_t sum = __reduce_add_sync(0xffffffffu, useful);
         if (lane == 0) {
-            s_useful[warp] = (unsigned long long)lo + ((unsigned long long)hi << 16);
+            s_useful[warp] = sum;
             s_longest[warp] = longest;
         }
     }

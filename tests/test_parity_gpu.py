@@ -174,7 +174,7 @@ def test_render_frames_leaves_room_for_other_callers(gpu):
     running (the GUI's screenshot thread, src/gui.rs:325) completes long before the animation does."""
     import threading
     import time
-    cfgs = [configs.c5_frame(150 + (k % 40)) for k in range(100)]
+    cfgs = [configs.c5_frame(150 + (k % 40)) for k in range(160)]
     small = configs.c1().with_(width=320, height=200)
     want = gpu.get_image(small)
     t_anim = {}
@@ -194,7 +194,7 @@ def test_render_frames_leaves_room_for_other_callers(gpu):
         if th.is_alive():
             during += 1   # this call started AND finished while the animation was still running
     th.join()
-    assert during >= 1, f"no concurrent frame completed during an animation of {t_anim['s']:.3f} s"
+    assert during >= 3, f"{during} concurrent frames completed during an animation of {t_anim['s']:.3f} s"
 
 
 def test_render_frames_strided_tiles_the_animation(gpu):
