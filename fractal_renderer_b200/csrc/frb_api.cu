@@ -46,6 +46,10 @@ constexpr uint32_t kMaxIterWarps = 16384;  // upper bound on resident warps of o
 // its default here.  A product build (no -DFRB_TUNING) reads nothing else: no environment variable, no hidden switch, the
 // defaults are compile-time constants.  The tuning build (`make tune` -> libfrb_tune.so, used by the sweeps under scripts/ and by
 // two tests that force rarely taken paths) makes them settable through frb_set_tuning().
+// Tile kernel shapes (frb_tile.cuh): 8 x 4 pixels per warp for images in device memory (best lane utilisation: C1 0.930 against
+// 0.914 for 16 x 2 and 0.884 for 32 x 1), 32 x 1 when the kernel's stores go straight to pinned host memory: a tile row is then
+// 96 contiguous bytes on the PCIe link instead of 24 (C1 end to end: 0.187 ms against 0.269; profiles/r2_tile_shapes.txt)
+constexpr int kTileDefaultW = 8, kTileHostW = 32, kTileDefaultWpc = 4;
 struct Tuning {
     int defer_b = 0;            // deferred kernel: iterations per block (0 = by iteration cap)
     int defer_nb = 0;           //                  blocks per trip      (0 = by iteration cap)
@@ -68,6 +72,8 @@ struct Tuning {
     int pool_max = 31;          //                  a drained warp with at most this many live lanes donates them (<= 31)
     int populate = 1;           // staging pipeline: first-touch the destination ahead of the copies
     int tile_smem_kb = 0;       // tile kernel: unused dynamic shared memory per CTA, to cap the CTAs resident per SM (experiments)
+    int tile_w = 0;                 // tile kernel: pixels per tile row (8 x 4, 16 x 2 or 32 x 1 pixels per warp; 0 = by destination)
+    int tile_wpc = kTileDefaultWpc; //              warps per CTA
 };
 #ifdef FRB_TUNING
 Tuning g_tuning;
@@ -107,7 +113,12 @@ struct StatSlot {
     unsigned long long stream_status;  // low word != 0: the streaming finisher gave up waiting (frb_stream.cuh)
     unsigned long long reserved[9];    // device words 3..11 (trace stamps, election, work counter, generation)
     unsigned long long stream_started; // device word 12: finisher CTAs that saw their frame start (0 = nothing was shaded)
+    unsigned long long reserved2[3];   // device words 13..15
+    unsigned long long tile_part[2 * frb::kTileStatsPairs];  // the tile kernel's spread (iterations, lane slots) counters
 };
+static_assert(offsetof(StatSlot, tile_part) == frb::kTileStatsWord * sizeof(unsigned long long), "StatSlot mirrors the device words");
+constexpr size_t kStatsBytes = 1024;  // device statistics block
+static_assert(sizeof(StatSlot) <= kStatsBytes, "device statistics block");
 
 struct Slot {
     cudaEvent_t ev_start = nullptr, ev_iter = nullptr, ev_shade = nullptr, ev_end = nullptr;
@@ -202,8 +213,8 @@ int ctx_init(DeviceCtx *c, int dev)
     for (auto &bs : c->sets) {
         CU(cudaEventCreateWithFlags(&bs.ev_guard, cudaEventDisableTiming));
         CU(cudaMalloc(&bs.queue, 256));
-        CU(cudaMalloc(&bs.stats, 256));
-        CU(cudaMemset(bs.stats, 0, 256));
+        CU(cudaMalloc(&bs.stats, kStatsBytes));
+        CU(cudaMemset(bs.stats, 0, kStatsBytes));
         CU(cudaMalloc(&bs.wm, (kMaxIterWarps + kMaxStageSlabs) * sizeof(uint32_t)));  // watermarks, then the finisher's slab counters
     }
     CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
@@ -457,6 +468,7 @@ struct Plan {
     uint32_t variant;
     bool fern;      // algo = BarnsleyFern: the per-pixel path is all black (calc/src/lib.rs:211); no iterate kernel runs
     int tile_form;  // tile kernel: 6- or 7-instruction iteration
+    bool tile_host; //              its stores go to pinned host memory (render_blocking: tile_alias)
     uint64_t tile_key;  // non-zero when AUTO chose the tile kernel
     int defer_b, defer_nb, defer_minb;  // deferred kernel: iterations per block, blocks per trip, CTA shape (index into kDeferShapes)
     uint64_t npix;
@@ -547,7 +559,7 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
     // short orbits, image wanted: the lock-step tile kernel (per-pixel costs of the refill kernels outweigh their lane
     // utilisation there).  It has no raw-result output (format 0 falls through), and its grid puts 8 rows on blockIdx.y.
     const uint32_t tile_max = (uint32_t)std::min(65535, std::max(0, tuning().tile_max));  // its statistics are 32-bit sums per CTA
-    const bool tile_fits = (p.rows + 7u) / 8u <= 65535u;
+    const bool tile_fits = p.rows <= 65535u;  // grid.y carries the tile rows
     plan->fern = cfg.algo == FRB_ALGO_BARNSLEY_FERN;  // get_recursive_pixel returns BLACK for it: nothing to iterate
     if (v == FRB_KERNEL_TILE && (format == 0 || plan->fern || !tile_fits || cfg.iterations > 65535u)) v = FRB_KERNEL_AUTO;
     plan->tile_key = 0;
@@ -564,6 +576,7 @@ int make_plan(DeviceCtx &c, const FrbConfig &cfg, const FrbShard &sh, uint32_t f
         }
     }
     plan->tile_form = form6_is_exact(cfg) ? 6 : 7;
+    plan->tile_host = false;
     if (v == FRB_KERNEL_AUTO || v == FRB_KERNEL_DEFER6) v = deferred_is_safe(cfg) ? FRB_KERNEL_DEFER6 : FRB_KERNEL_DENSE6;
     if (v == FRB_KERNEL_DENSE6 && !form6_is_exact(cfg)) v = FRB_KERNEL_STREAM7;
     plan->variant = v;
@@ -645,11 +658,29 @@ int launch_iterate(DeviceCtx &c, const Plan &plan, const RenderParams &p, cudaSt
     }
     if (plan.variant == FRB_KERNEL_TILE) {
         // iterates AND shades: the caller skips the shade kernel
-        dim3 grid((p.width + frb::kTileW - 1) / frb::kTileW, (p.rows + frb::kTileH - 1) / frb::kTileH);
-        if (grid.y > 65535u) return fail(FRB_ERR_TOO_LARGE, "tile kernel: %u rows exceed the grid's y extent", p.rows);
         const size_t dyn = (size_t)std::min(44, std::max(0, tuning().tile_smem_kb)) << 10;
-        if (plan.tile_form == 6) frb::frb_iterate_tile_kernel<6><<<grid, frb::kTileW * frb::kTileH, dyn, st>>>(p);
-        else frb::frb_iterate_tile_kernel<7><<<grid, frb::kTileW * frb::kTileH, dyn, st>>>(p);
+        const int tile_w = tuning().tile_w > 0 ? tuning().tile_w : (plan.tile_host ? kTileHostW : kTileDefaultW);
+        const int key = tile_w * 100 + tuning().tile_wpc * 10 + (plan.tile_form == 6 ? 6 : 7);
+#define FRB_TILE_CASE(TW, WPC)                                                                              \
+    case (TW) * 100 + (WPC) * 10 + 6:                                                                       \
+    case (TW) * 100 + (WPC) * 10 + 7: {                                                                     \
+        dim3 grid((p.width + (TW) * (WPC) - 1) / ((TW) * (WPC)), (p.rows + 32 / (TW) - 1) / (32 / (TW)));   \
+        if (grid.y > 65535u) return fail(FRB_ERR_TOO_LARGE, "tile kernel: %u rows exceed the grid's y extent", p.rows); \
+        if (plan.tile_form == 6) frb::frb_iterate_tile_kernel<6, TW, WPC><<<grid, 32 * (WPC), dyn, st>>>(p); \
+        else frb::frb_iterate_tile_kernel<7, TW, WPC><<<grid, 32 * (WPC), dyn, st>>>(p);                     \
+        break;                                                                                              \
+    }
+        switch (key) {
+            FRB_TILE_CASE(kTileDefaultW, kTileDefaultWpc) FRB_TILE_CASE(kTileHostW, kTileDefaultWpc)
+#ifdef FRB_TUNING
+            FRB_TILE_CASE(8, 1) FRB_TILE_CASE(8, 2) FRB_TILE_CASE(8, 8)
+            FRB_TILE_CASE(16, 1) FRB_TILE_CASE(16, 2) FRB_TILE_CASE(16, 4)
+            FRB_TILE_CASE(32, 1) FRB_TILE_CASE(32, 2)
+#endif
+        default:
+            return fail(FRB_ERR_INVALID, "no tile kernel for %d-pixel-wide tiles, %d warps per CTA", tile_w, tuning().tile_wpc);
+        }
+#undef FRB_TILE_CASE
         return FRB_OK;
     }
     const uint32_t warps_per_block = frb::kIterateThreads / 32;
@@ -777,6 +808,7 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
     }
     CU(cudaEventRecord(slot.ev_shade, st));
     if (plan.npix > 0) CU(cudaMemcpyAsync(slot.host, c.b().stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, st));
+    else memset(slot.host, 0, sizeof(StatSlot));  // an empty shard: nothing ran, nothing to report (not the slot's last frame)
     CU(cudaGetLastError());
     return FRB_OK;
 }
@@ -1014,6 +1046,11 @@ int harvest(DeviceCtx &c, Slot &slot, FrbStats *out, double total_ms)
     s.pixels = slot.pixels;
     s.iterations = slot.host->iterations;
     s.lane_iterations = slot.host->lane_iterations;
+    if (slot.variant == FRB_KERNEL_TILE)
+        for (uint32_t k = 0; k < frb::kTileStatsPairs; ++k) {
+            s.iterations += slot.host->tile_part[2 * k];
+            s.lane_iterations += slot.host->tile_part[2 * k + 1];
+        }
     if (slot.tile_key != 0 && slot.pixels >= (1u << 16) && s.lane_iterations > 0 &&
         (double)s.iterations < kTileMinUtilisation * (double)s.lane_iterations) {
         c.tile_bad_key.store(slot.tile_key);
@@ -1426,6 +1463,7 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
             CU(cudaMemcpyAsync(slot->host, c->b().stats, sizeof(StatSlot), cudaMemcpyDeviceToHost, c->stream));
         }
     } else if (tile_alias) {
+        plan.tile_host = true;
         if (int rc = enqueue(*c, plan, tile_alias, c->stream, &slot)) return rc;
     } else if (sliced) {
         // every slab is one more persistent launch (~0.1 ms of ramp and tail) but exposes a smaller last copy: 4 slabs up to
@@ -1725,7 +1763,8 @@ static int warm_device(int d)
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(d));
     const void *common[] = {(const void *)frb::frb_coord_tables_kernel, (const void *)frb::frb_shade_kernel,
-                            (const void *)frb::frb_finish_stream_kernel, (const void *)frb::frb_iterate_tile_kernel<6>,
+                            (const void *)frb::frb_finish_stream_kernel, (const void *)frb::frb_iterate_tile_kernel<6, kTileDefaultW, kTileDefaultWpc>,
+                            (const void *)frb::frb_iterate_tile_kernel<6, kTileHostW, kTileDefaultWpc>,
                             (const void *)frb::frb_resolve_kernel, (const void *)frb::frb_sum_iterations_kernel};
     for (const void *k : common)
         if (int rc = preload_kernel(*c, k)) return rc;
@@ -1788,7 +1827,7 @@ int frb_set_tuning(const char *name, int64_t value)
         {"stream", &Tuning::stream},         {"stream_gen_polls", &Tuning::stream_gen_polls},
         {"stream_rows", &Tuning::stream_rows}, {"stream_ctas", &Tuning::stream_ctas},
         {"slabs", &Tuning::slabs},           {"no_slab", &Tuning::no_slab},
-        {"stage", &Tuning::stage},           {"copy_threads", &Tuning::copy_threads}, {"populate", &Tuning::populate}, {"tile_smem_kb", &Tuning::tile_smem_kb},
+        {"stage", &Tuning::stage},           {"copy_threads", &Tuning::copy_threads}, {"populate", &Tuning::populate}, {"tile_smem_kb", &Tuning::tile_smem_kb}, {"tile_w", &Tuning::tile_w}, {"tile_wpc", &Tuning::tile_wpc},
         {"end_chunk", &Tuning::end_chunk},   {"pool", &Tuning::pool},
         {"pool_max", &Tuning::pool_max},     {"tile_direct", &Tuning::tile_direct},
         {"hugepage", &Tuning::hugepage},

@@ -128,6 +128,7 @@ __global__ void frb_coord_tables_kernel(const __grid_constant__ RenderParams p)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t < 16) p.queue[t] = 0u;  // one counter per row slab (frb_api.cu: enqueue_sliced)
+    if (t < 64) p.stats[16 + t] = 0ull;  // the tile kernel's spread counters (frb_tile.cuh: kTileStatsWord, kTileStatsPairs)
     if (t == 0) {
         p.stats[0] = 0ull;
         p.stats[1] = 0ull;

@@ -15,19 +15,23 @@
 
 namespace frb {
 
-constexpr int kTileW = 32, kTileH = 8;  // pixels per CTA: 8 warps, warp w covers columns (w % 4) * 8 .. + 8, rows (w / 4) * 4 .. + 4
+constexpr uint32_t kTileStatsWord = 16u;   // first word of p.stats that holds the tile kernel's spread counters
+constexpr uint32_t kTileStatsPairs = 32u;  // (useful iterations, lane slots) pairs
 
-template <int FORM>
-__global__ void __launch_bounds__(kTileW * kTileH)
+// TW x (32 / TW) pixels per warp, WPC warps side by side per CTA.  Warps share nothing — no shared memory, no barrier — so the
+// CTA is only the granularity at which the SM gets warp slots back: with 8-warp CTAs and a barrier before the stores (the
+// first version) a tile on the rim of the set kept seven finished warps resident behind its one long orbit, and the FP64
+// pipe starved with the SM nominally full (ncu: 44 resident warps, pipe 61 % busy, 2.2 barrier stalls per issue).
+template <int FORM, int TW, int WPC>
+__global__ void __launch_bounds__(32 * WPC)
 frb_iterate_tile_kernel(const __grid_constant__ RenderParams p)
 {
-    __shared__ __align__(16) uint8_t stage[kTileH][kTileW * 4];
-    __shared__ uint32_t s_useful[kTileH];
-    __shared__ uint32_t s_longest[kTileH];
-    const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-    const uint32_t tx = (warp & 3u) * 8u + (lane & 7u), ty = (warp >> 2) * 4u + (lane >> 3);
-    const uint32_t x = blockIdx.x * kTileW + tx;
-    const uint32_t lr = blockIdx.y * kTileH + ty;  // row of this launch; p.resolve_row0 = its first row within the shard
+    constexpr uint32_t TH = 32u / TW;
+    const unsigned lane = threadIdx.x & 31u;
+    const uint32_t tx = lane % TW, ty = lane / TW;
+    const uint32_t x0 = (blockIdx.x * WPC + (threadIdx.x >> 5)) * TW;  // first column of the warp's tile
+    const uint32_t x = x0 + tx;
+    const uint32_t lr = blockIdx.y * TH + ty;  // row of this launch; p.resolve_row0 = its first row within the shard
     const bool valid = x < p.width && lr < p.rows;
 
     uint32_t count = 0;
@@ -56,7 +60,7 @@ frb_iterate_tile_kernel(const __grid_constant__ RenderParams p)
         // an early hit escapes; and escaped lanes idle to the end of the tile anyway).
         uint32_t i = 0;
         for (;;) {
-            Orbit pre = o;
+            Orbit pre;  // written by the loop on the exits that use it
             uint32_t k;
             // Written in PTX: from C++ the compiler recomputed squares on both sides of the filter branch and carried the
             // exit index through the loop (26 FP64 and 12 other instructions per four iterations instead of 24 and 11).
@@ -116,7 +120,7 @@ frb_iterate_tile_kernel(const __grid_constant__ RenderParams p)
                  "mov.u32 %9, 2;\n"                                                                                         \
                  "FRB_DONE:\n\t"                                                                                            \
                  "}"                                                                                                        \
-                 : "+d"(o.x), "+d"(o.y), "+d"(o.a), "+d"(o.b), "+d"(pre.x), "+d"(pre.y), "+d"(pre.a), "+d"(pre.b), "+r"(i), \
+                 : "+d"(o.x), "+d"(o.y), "+d"(o.a), "+d"(o.b), "=d"(pre.x), "=d"(pre.y), "=d"(pre.a), "=d"(pre.b), "+r"(i), \
                    "=r"(k)                                                                                                  \
                  : "d"(o.cr), "d"(o.ci), "r"(n4), "r"(filter_hi))
             if (FORM == 6) FRB_TILE_LOOP(FRB_STEP6);
@@ -158,34 +162,18 @@ frb_iterate_tile_kernel(const __grid_constant__ RenderParams p)
     // no barrier between a warp's last iteration and its shading
     const uint32_t c = valid ? shade_pixel<true>(p, count, make_double2(o.x, o.y), g_log2_table) : 0u;
 
-    // statistics: loop-body executions (i + 1 | iterations) and the lane slots the lock-step warps spent (32 x the longest orbit),
-    // summed over the CTA first: two same-address atomics per WARP (65 000 warps on C1) serialise in the L2 for longer than
-    // the frame takes to iterate.  The kernel only runs caps below 2^16 (frb_api.cu: make_plan), so a warp's sum fits a word.
+    // statistics: loop-body executions (i + 1 | iterations) and the lane slots the lock-step warp spent (32 x its longest orbit).
+    // Two same-address atomics per warp (65 000 warps on C1) would serialise in the L2 for longer than the frame takes to
+    // iterate, so the warps spread them over 32 pairs of counters that K0 cleared and the host adds up (frb_api.cu: harvest).
+    // The kernel only runs caps below 2^16 (make_plan), so a warp's sum fits a word.
     {
         const uint32_t useful = (valid && p.iterations != 0u) ? min(count, p.iterations - 1u) + 1u : 0u;
         const uint32_t longest = __reduce_max_sync(0xffffffffu, useful);
         const uint32_t sum = __reduce_add_sync(0xffffffffu, useful);
-        if (lane == 0) {
-            s_useful[warp] = sum;
-            s_longest[warp] = longest;
-        }
-    }
-    if (p.format != 4u) {
-        stage[ty][tx * 3 + 0] = (uint8_t)c;
-        stage[ty][tx * 3 + 1] = (uint8_t)(c >> 8);
-        stage[ty][tx * 3 + 2] = (uint8_t)(c >> 16);
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned long long useful = 0, slots = 0;
-#pragma unroll
-        for (int w = 0; w < kTileH; ++w) {
-            useful += s_useful[w];
-            slots += 32ull * s_longest[w];
-        }
-        if (useful != 0ull) {
-            atomicAdd(p.stats + 0, useful);
-            atomicAdd(p.stats + 1, slots);
+        if (lane == 0 && sum != 0u) {
+            unsigned long long *part = p.stats + kTileStatsWord + 2u * ((blockIdx.x + 5u * blockIdx.y + (threadIdx.x >> 5)) & (kTileStatsPairs - 1u));
+            atomicAdd(part, (unsigned long long)sum);
+            atomicAdd(part + 1, 32ull * longest);
         }
     }
 
@@ -193,23 +181,24 @@ frb_iterate_tile_kernel(const __grid_constant__ RenderParams p)
         if (valid) reinterpret_cast<uint32_t *>(p.out)[(size_t)lr * p.width + x] = c | 0xff000000u;
         return;
     }
-    // RGB24: the CTA's 8 row segments of up to 96 bytes.  Full segments of a frame whose width is a multiple of 4 start on a
-    // word boundary (row * width * 3 + 96 * blockIdx.x): 24 word stores per row, consecutive threads on consecutive words.
-    const uint32_t x0 = blockIdx.x * kTileW;
-    const uint32_t seg = min((uint32_t)kTileW, p.width - x0) * 3u;  // bytes per row segment
-    if (seg == 96u && (p.width & 3u) == 0u && (reinterpret_cast<uintptr_t>(p.out) & 3u) == 0u) {
-        if (threadIdx.x < (uint32_t)kTileH * 24u) {
-            const uint32_t r = threadIdx.x / 24u, w = threadIdx.x - r * 24u;
-            const uint32_t row = blockIdx.y * kTileH + r;
-            if (row < p.rows)
-                reinterpret_cast<uint32_t *>(p.out + ((size_t)row * p.width + x0) * 3u)[w] = reinterpret_cast<const uint32_t *>(stage[r])[w];
-        }
+    // RGB24: a tile row is 3 TW bytes = 3 TW / 4 words.  Word j of the row takes its bytes from pixels p0 = 4j / 3 and p0 + 1
+    // (two shuffles and a funnel shift), and lane ty * TW + j stores it: consecutive lanes, consecutive words.  Needs the row
+    // segment to start on a word boundary: width a multiple of 4 (x0 is one of TW) and an aligned image.
+    const bool valid_row = lr < p.rows;
+    if (x0 + TW <= p.width && (p.width & 3u) == 0u && (reinterpret_cast<uintptr_t>(p.out) & 3u) == 0u) {
+        const uint32_t p0 = (tx * 4u) / 3u, sh = (tx * 4u - p0 * 3u) * 8u;
+        const uint32_t c0 = __shfl_sync(0xffffffffu, c, (int)(ty * TW + p0));
+        const uint32_t c1 = __shfl_sync(0xffffffffu, c, (int)(ty * TW + min(p0 + 1u, (uint32_t)TW - 1u)));
+        const uint32_t word = __funnelshift_r(c0 | (c1 << 24), c1 >> 8, sh);
+        if (tx < (3u * TW) / 4u && valid_row)
+            reinterpret_cast<uint32_t *>(p.out + ((size_t)lr * p.width + x0) * 3u)[tx] = word;
         return;
     }
-    for (uint32_t k = threadIdx.x; k < (uint32_t)kTileH * 96u; k += blockDim.x) {
-        const uint32_t r = k / 96u, b = k - r * 96u;
-        const uint32_t row = blockIdx.y * kTileH + r;
-        if (b < seg && row < p.rows) p.out[((size_t)row * p.width + x0) * 3u + b] = stage[r][b];
+    if (valid) {
+        uint8_t *q = p.out + ((size_t)lr * p.width + x) * 3u;
+        q[0] = (uint8_t)c;
+        q[1] = (uint8_t)(c >> 8);
+        q[2] = (uint8_t)(c >> 16);
     }
 }
 

@@ -381,6 +381,31 @@ for it, exposure in cases:
 """)
 
 
+def test_tile_kernel_shapes_agree(gpu):
+    """The tile kernel's other shapes (tuning build: 8x4, 16x2, 32x1 pixels per warp, 1-8 warps per CTA) produce the bytes and
+    the statistics of the product's shape on ragged sizes (width not a multiple of 4 or of the tile, few rows), both formats,
+    sharded or not."""
+    from tune_run import run_with_tuning_build
+    run_with_tuning_build(r"""
+frb.set_kernel_variant(frb.KERNEL_TILE)
+cases = [configs.c1().with_(width=640, height=360), configs.c1().with_(width=333, height=77, iterations=100),
+         configs.c3().with_(width=516, height=130, iterations=200), configs.c1().with_(width=8, height=3, iterations=60)]
+for cfg in cases:
+    for shard in (frb.Shard(), frb.Shard(1, 3, 16)):
+        for fmt in (frb.FRB_RGB24, frb.FRB_RGBA32):
+            ref = None
+            for tw, wpc in ((8, 4), (8, 1), (8, 8), (16, 2), (32, 1), (32, 4)):
+                frb.set_tuning("tile_w", tw); frb.set_tuning("tile_wpc", wpc)
+                img = frb.render_shard(cfg, shard, fmt)
+                st = frb.last_stats()
+                assert st["kernel_variant"] == frb.KERNEL_TILE
+                if ref is None:
+                    ref, ref_it = img, st["iterations"]
+                assert np.array_equal(img, ref), (cfg.width, cfg.height, tw, wpc, fmt)
+                assert st["iterations"] == ref_it
+""")
+
+
 def test_tile_kernel_backs_off_on_scenes_with_poor_lane_utilisation(gpu):
     """Julia dust with a short cap: orbit lengths inside an 8x4 tile differ wildly, the lock-step kernel reports its lane
     utilisation, and the library keeps the lane-refill kernel for the following frames of that scene (same bytes either way)."""
