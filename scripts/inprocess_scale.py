@@ -1,12 +1,11 @@
 """In-process multi-GPU: frb_render(device=-1) — the call a Rust `get_image` shim makes — on 1, 2, 4, 8 devices of one box.
 Interleaved 16-row bands, one stream set per device, strided copies into ONE pinned host image; wall clock per blocking call.
-usage (GPU box): python scripts/inprocess_scale.py [C2 C4 C1]"""
+usage (GPU box): python scripts/inprocess_scale.py [C2 C4 C1 C3]"""
 import json
 import sys
 import time
 
 import numpy as np
-import torch
 
 sys.path.insert(0, ".")
 import fractal_renderer_b200 as frb
@@ -18,10 +17,10 @@ ndev = frb.device_count()
 out = {}
 for name in which:
     cfg = cfgs[name]
-    buf = torch.empty(cfg.width * cfg.height * 3, dtype=torch.uint8).pin_memory().numpy()
+    buf = frb.pinned_empty(cfg.width * cfg.height * 3)
     ref = None
     for n in [k for k in (1, 2, 4, 8) if k <= ndev]:
-        frb.init((1 << n) - 1)
+        frb.init_list(list(range(n)))
         steps = 3 if name == "C4" else 30
         for _ in range(2):
             frb.get_image_into(cfg, buf, frb.FRB_RGB24, device=-1)
