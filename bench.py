@@ -163,6 +163,33 @@ def cpu_sample_config(args, cfg_or_list):
     return cfg_or_list, "the frame"
 
 
+def server_latency(device):
+    """Median round trip of the headless frame server on 1920x1080 views, a zoom step per frame (scripts/server_latency.py)."""
+    import numpy as np
+    from fractal_renderer_b200 import configs
+    from fractal_renderer_b200.interactive import FrameServer, ViewState
+    views = {"C1 view it256": configs.c1(), "C2 view it4000": configs.c2().with_(width=1920, height=1080)}
+    out = {"note": "request -> poll of the RGBA frame, ms; poll copies the frame into a fresh array, acquire hands out the server's own buffer"}
+    with FrameServer(device=device) as srv:
+        for name, cfg in views.items():
+            view = ViewState(cfg)
+            for _ in range(3):
+                srv.request(view.config)
+                srv.poll(10000)
+            for copy in (True, False):
+                lat = []
+                for k in range(30):
+                    view.apply_scroll(1.0 if k % 2 else -1.0)
+                    t = time.perf_counter()
+                    srv.request(view.config)
+                    frame = srv.poll(10000, copy=copy)
+                    lat.append((time.perf_counter() - t) * 1e3)
+                    if frame is None:
+                        raise RuntimeError("frame server timed out")
+                out[f"{name} [{'poll' if copy else 'acquire'}]"] = {"median_ms": round(float(np.median(lat)), 3), "p95_ms": round(float(np.percentile(lat, 95)), 3)}
+    return out
+
+
 def cpu_baseline(args, cfg) -> dict:
     cores = host_threads()
     cfg1, what = cpu_sample_config(args, cfg)
@@ -568,6 +595,12 @@ def main():
         b.close()
         return
     sampler.stop()
+    # (f)1 frame server round trips (request -> render thread -> RGBA frame), the GUI loop of src/gui.rs:37-117 without the window
+    if not args.no_extras and world == 1:
+        try:
+            extra["server_latency"] = server_latency(local)
+        except Exception as e:  # evidence, not the measurement
+            extra["server_latency"] = f"FAILED: {e}"
 
     # ---------------- roofline of the dominant kernel (iterate) ----------------
     it_ms = dev["iterate_ms"]
@@ -576,7 +609,7 @@ def main():
     peak_tflops = peak["dfma_per_s"] * 2 / 1e12
     kv = dev["variant"]
     form = {frb.KERNEL_TILE: 6, frb.KERNEL_DEFER6: 6, frb.KERNEL_DENSE6: 6, frb.KERNEL_STREAM7: 7}.get(kv, 11)
-    kname = {frb.KERNEL_TILE: "frb_iterate_tile_kernel<6> (iterate + shade)", frb.KERNEL_DEFER6: "frb_iterate_deferred_kernel<6>",
+    kname = {frb.KERNEL_TILE: "frb_iterate_tile_kernel<6, 8, 4> (iterate + shade)", frb.KERNEL_DEFER6: "frb_iterate_deferred_kernel<6>",
              frb.KERNEL_DENSE6: "frb_iterate_stream_kernel<6>", frb.KERNEL_STREAM7: "frb_iterate_stream_kernel<7>"}.get(kv, "frb_iterate_simple_kernel")
     traffic, traffic_note = None, None
     try:
@@ -630,7 +663,9 @@ def main():
             "timed_region_s": round(dev["ms_total"] * 1e-3, 3),
             "partition": ("one frame, interleaved 16-row bands" if strong else "one whole frame per rank") if world > 1 else "single GPU",
             "kernel": frb.KERNEL_NAMES[kv], "format": "RGB24",
-            "l2": "not flushed: no reusable input (48 KB of coordinate tables are recomputed every frame); each frame writes 207 MB (> 126 MB L2)",
+            "l2": "not flushed: no reusable input (%d KB of coordinate tables are recomputed every frame); each frame writes %.0f MB of new data (%s)" % (
+                (cfg.width + cfg.height) * 8 // 1024, cfg.width * cfg.height * (3 if kv == frb.KERNEL_TILE else 23) / 1e6,
+                "3 B/px image; smaller than the 126 MB L2, nothing is read back" if kv == frb.KERNEL_TILE else "20 B/px provisional records + 3 B/px image"),
         },
         "ms_per_frame": round(dev["ms_per_frame"], 4),
         "e2e": {"value": round(e2e["g_iter_s"], 2), "unit": "G iter/s", "h2d_bytes_per_step": 104 * e2e["reps"], "d2h_bytes_per_step": (d2h + 16 * (world if strong else 1)) * e2e["reps"],
