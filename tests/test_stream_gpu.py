@@ -216,3 +216,37 @@ def test_library_pinned_allocations_take_the_streamed_path(gpu):
     finally:
         _lib.check(lib.frb_host_unregister(ctypes.c_void_p(view.ctypes.data)))
     assert lib.frb_host_register(None, 16) == -2
+
+
+TILE_CASES = {
+    "C1": configs.c1(),                                             # 2 Mpx: staged (pageable) / direct (pinned)
+    "C1_odd": configs.c1().with_(width=1921, height=700),           # width not a multiple of 4: byte stores
+    "C1_small": configs.c1().with_(width=640, height=360),          # below the staging threshold: plain path
+    "julia_300": configs.c3().with_(width=1600, height=900, iterations=300),
+}
+
+
+@pytest.mark.parametrize("fmt", [3, 4])
+@pytest.mark.parametrize("name", sorted(TILE_CASES))
+def test_tile_frames_equal_on_every_destination(gpu, name, fmt):
+    """The tile kernel's three host paths — pinned destination (its stores go over PCIe, 32x1 tiles), pageable destination (the
+    same into the library's staging, copy threads after), device destination (8x4 tiles) — and a 3-way shard split of each."""
+    cfg = TILE_CASES[name]
+    gpu.set_kernel_variant(gpu.KERNEL_TILE)
+    try:
+        ref, st = render_device(gpu, cfg, fmt)
+        assert st["kernel_variant"] == gpu.KERNEL_TILE
+        got_p = render_ordinary(gpu, cfg, fmt)
+        assert gpu.last_stats()["iterations"] == st["iterations"]
+        assert np.array_equal(got_p, ref), f"{name}: pageable destination differs in {np.count_nonzero(got_p != ref)} bytes"
+        got_h, st_h = render_pinned(gpu, cfg, fmt)
+        assert np.array_equal(got_h, ref), f"{name}: pinned destination differs in {np.count_nonzero(got_h != ref)} bytes"
+        assert st_h["iterations"] == st["iterations"]
+        whole = np.zeros_like(ref)
+        for k in range(3):
+            sh = gpu.Shard(k, 3, 16)
+            part = render_ordinary(gpu, cfg, fmt, sh)
+            whole[sh.image_rows(cfg.height)] = part
+        assert np.array_equal(whole, ref), name
+    finally:
+        gpu.set_kernel_variant(gpu.KERNEL_AUTO)
