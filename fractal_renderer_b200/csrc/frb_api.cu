@@ -121,7 +121,8 @@ constexpr size_t kStatsBytes = 1024;  // device statistics block
 static_assert(sizeof(StatSlot) <= kStatsBytes, "device statistics block");
 
 struct Slot {
-    cudaEvent_t ev_start = nullptr, ev_iter = nullptr, ev_shade = nullptr, ev_end = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_k0 = nullptr, ev_iter = nullptr, ev_shade = nullptr, ev_end = nullptr;
+    bool have_k0 = false;  // ev_k0 (after the table kernel) was recorded for this frame: iterate_ms is the iterate kernel alone
     StatSlot *host = nullptr;  // pinned
     uint64_t pixels = 0;
     uint32_t launches = 0;
@@ -226,6 +227,7 @@ int ctx_init(DeviceCtx *c, int dev)
     for (auto &s : c->slots) {
         CU(cudaEventCreate(&s.ev_start));
         CU(cudaEventCreate(&s.ev_iter));
+        CU(cudaEventCreate(&s.ev_k0));
         CU(cudaEventCreate(&s.ev_shade));
         CU(cudaEventCreate(&s.ev_end));
         CU(cudaMallocHost(&s.host, sizeof(StatSlot)));
@@ -259,6 +261,7 @@ void ctx_destroy(DeviceCtx *c)
         for (auto &s : c->slots) {
             if (s.ev_start) cudaEventDestroy(s.ev_start);
             if (s.ev_iter) cudaEventDestroy(s.ev_iter);
+            if (s.ev_k0) cudaEventDestroy(s.ev_k0);
             if (s.ev_shade) cudaEventDestroy(s.ev_shade);
             if (s.ev_end) cudaEventDestroy(s.ev_end);
             if (s.host) cudaFreeHost(s.host);
@@ -785,11 +788,14 @@ int enqueue(DeviceCtx &c, Plan &plan, uint8_t *dev_out, cudaStream_t st, Slot **
     if (c.b().have_guard && c.b().last_stream != st) CU(cudaStreamWaitEvent(st, c.b().ev_guard, 0));
 
     CU(cudaEventRecord(slot.ev_start, st));
+    slot.have_k0 = false;
     if (plan.npix > 0) {
         const uint32_t n = std::max(p.width, p.height);
         frb::frb_coord_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
         slot.launches++;
         if (!plan.fern) {
+            CU(cudaEventRecord(slot.ev_k0, st));
+            slot.have_k0 = true;
             if (int rc = launch_iterate(c, plan, p, st)) return rc;
             slot.launches += (plan.variant == FRB_KERNEL_DEFER6 && p.records == 0u) ? 2 : 1;  // raw DEFER6 = iterate + resolve
         } else {
@@ -904,6 +910,8 @@ int enqueue_streamed(DeviceCtx &c, Plan &plan, uint8_t *dst, cudaStream_t st, Sl
 
     const uint32_t n = std::max(p.width, p.height);
     frb::frb_coord_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
+    CU(cudaEventRecord(slot.ev_k0, st));
+    slot.have_k0 = true;
     if (int rc = launch_iterate(c, plan, p, st)) return rc;
     CU(cudaEventRecord(slot.ev_iter, st));
     CU(cudaStreamWaitEvent(st, c.ev_join[p.stream_gen & 1u], 0));
@@ -977,6 +985,7 @@ int enqueue_sliced(DeviceCtx &c, Plan &plan, uint8_t *host_out, int nslabs, Slot
     cudaStream_t st = c.stream;
     if (c.b().have_guard && c.b().last_stream != st) CU(cudaStreamWaitEvent(st, c.b().ev_guard, 0));
     CU(cudaEventRecord(slot.ev_start, st));
+    slot.have_k0 = false;
     const uint32_t n = std::max(p.width, p.height);
     frb::frb_coord_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
     slot.launches++;
@@ -1057,7 +1066,7 @@ int harvest(DeviceCtx &c, Slot &slot, FrbStats *out, double total_ms)
         c.tile_bad_frames.store(kTileBackoffFrames);
     }
     float ms = 0.f;
-    CU(cudaEventElapsedTime(&ms, slot.ev_start, slot.ev_iter));
+    CU(cudaEventElapsedTime(&ms, slot.have_k0 ? slot.ev_k0 : slot.ev_start, slot.ev_iter));  // the iterate kernel alone where K0 has its own mark
     s.iterate_ms = ms;
     CU(cudaEventElapsedTime(&ms, slot.ev_iter, slot.ev_shade));
     s.shade_ms = ms;
