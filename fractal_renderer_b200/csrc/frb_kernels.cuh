@@ -449,6 +449,10 @@ __device__ const double2 g_log2_table[128] = {
 #include "frb_log2_table.inc"
 };
 
+// degree-6 Taylor coefficients of log2(1 + r) from r^6 down to r^1, then 2^52 + 1023 (the exponent bias of the 2^52 trick)
+__constant__ double c_log2_poly[7] = {-0.24044917348149392, 0.28853900817779266, -0.36067376022224085, 0.48089834696298783,
+                                      -0.7213475204444817,  1.4426950408889634,  4503599627371519.0};
+
 __device__ __forceinline__ void load_log2_table(double2 *dst)  // dst: 128 entries of shared memory; caller syncs
 {
     for (unsigned i = threadIdx.x; i < 128u; i += blockDim.x) dst[i] = g_log2_table[i];
@@ -464,12 +468,13 @@ __device__ __forceinline__ double shade_log2(double x, const double2 *tbl)
     const double2 t = GLOBAL_TABLE ? __ldg(tbl + ((hi >> 13) & 127u)) : tbl[(hi >> 13) & 127u];
     const double r = fma(m, t.x, -1.0);
     // biased exponent -> double without a conversion instruction: the bits of 2^52 + E, minus (2^52 + 1023)
-    const double e = __dsub_rn(__hiloint2double(0x43300000, (int)(hi >> 20)), 4503599627371519.0);
-    double q = fma(r, -0.24044917348149392, 0.28853900817779266);
-    q = fma(r, q, -0.36067376022224085);
-    q = fma(r, q, 0.48089834696298783);
-    q = fma(r, q, -0.7213475204444817);
-    q = fma(r, q, 1.4426950408889634);
+    // the coefficients come from the constant bank as instruction operands; as literals each cost two UMOVs per use site
+    const double e = __dsub_rn(__hiloint2double(0x43300000, (int)(hi >> 20)), c_log2_poly[6]);
+    double q = fma(r, c_log2_poly[0], c_log2_poly[1]);
+    q = fma(r, q, c_log2_poly[2]);
+    q = fma(r, q, c_log2_poly[3]);
+    q = fma(r, q, c_log2_poly[4]);
+    q = fma(r, q, c_log2_poly[5]);
     return fma(r, q, __dadd_rn(e, t.y));
 }
 
