@@ -1499,6 +1499,7 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
         job->shard_count = sh.count;
         const int helpers = g_copy.helpers();
         job->running.store(helpers + 1);
+        advise_huge_pages(framed ? host_out : dst0, framed ? row_bytes * cfg.height : plan.out_bytes);
         job->plan_populate();
         plan.tile_host = true;
         int rc = enqueue(*c, plan, tile_stage->p, c->stream, &slot);
