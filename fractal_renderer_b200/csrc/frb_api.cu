@@ -2308,12 +2308,24 @@ int frb_render_device_async(const FrbConfig *cfg, const FrbShard *shard, void *d
     if (!c) return tl_code;
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+    // Renders issued on two different caller streams use the two sets of device buffers (tables, records, queue, statistics),
+    // so they can overlap like the frames of frb_render_frames: the next frame's persistent CTAs start on every SM the moment
+    // the previous frame's CTA leaves it, and its shade kernel runs beside them.  A stream keeps the set it used last; a new
+    // stream takes the other one.  Same stream, or the library's own: set 0, strictly in order, as before.
+    int set = 0;
+    if (c->sets[1].have_guard && c->sets[1].last_stream == st) set = 1;
+    else if (c->sets[0].have_guard && c->sets[0].last_stream != st && stream != nullptr) set = 1;
+    struct SetGuard {
+        DeviceCtx *c;
+        ~SetGuard() { c->cur_set = 0; }
+    } set_guard{c};
+    c->cur_set = set;
     Plan plan;
     if (int rc = make_plan(*c, *cfg, s, format, &plan)) return rc;
     if (out_len < plan.out_bytes) return fail(FRB_ERR_INVALID, "output buffer too small: %zu < %zu bytes", out_len, plan.out_bytes);
     if (plan.out_bytes && !dev_out) return fail(FRB_ERR_INVALID, "null device output buffer");
     if (((uintptr_t)dev_out & 15u) != 0) return fail(FRB_ERR_INVALID, "device output buffer must be 16-byte aligned");
-    cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
     const double t0 = now_ms();
     Slot *slot = nullptr;
     if (int rc = enqueue(*c, plan, (uint8_t *)dev_out, st, &slot)) return rc;

@@ -250,3 +250,27 @@ def test_tile_frames_equal_on_every_destination(gpu, name, fmt):
         assert np.array_equal(whole, ref), name
     finally:
         gpu.set_kernel_variant(gpu.KERNEL_AUTO)
+
+
+def test_device_async_on_two_streams_overlaps_and_stays_exact(gpu):
+    """frb_render_device_async on two caller streams: the library gives each stream its own set of device buffers, so frames of
+    different scenes may overlap on the device (bench.py's device-resident arm).  Every image must be the one the scene gives alone,
+    whatever the interleaving, including a return to a single stream afterwards."""
+    scenes = [configs.c2().with_(width=1200, height=900), configs.c3().with_(width=1024, height=1024),
+              configs.c1().with_(iterations=600), configs.c2().with_(width=1000, height=700, iterations=900)]
+    refs = [render_device(gpu, c, 3)[0] for c in scenes]
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    outs = [[torch.full((r.size + 64,), 0x5A, dtype=torch.uint8, device="cuda") for r in refs] for _ in streams]
+    for rep in range(3):
+        for k, cfg in enumerate(scenes):
+            for s, st in enumerate(streams):
+                j = (k + s) % len(scenes)   # the two streams render different scenes at the same time
+                gpu.render_device_async(scenes[j], outs[s][j].data_ptr(), refs[j].size, 3, device=0, stream=st.cuda_stream)
+    torch.cuda.synchronize()
+    for s in range(2):
+        for j, r in enumerate(refs):
+            got = outs[s][j][:r.size].cpu().numpy().reshape(r.shape)
+            assert np.array_equal(got, r), f"stream {s}, scene {j}: {np.count_nonzero(got != r)} bytes differ"
+    for j, cfg in enumerate(scenes):   # statistics of the last frames are still readable, and a single stream still works
+        got, st = render_device(gpu, cfg, 3)
+        assert np.array_equal(got, refs[j])
