@@ -40,6 +40,7 @@ def render_device(frb, cfg, fmt, shard=None):
     dev = torch.full((n + 64,), 0x5A, dtype=torch.uint8, device="cuda")
     frb.render_device_async(cfg, dev.data_ptr(), n, fmt, device=0, shard=sh)
     st = frb.sync_stats()
+    assert bool((dev[n:] == 0x5A).all()), "the kernel wrote past the end of the image"
     return dev[:n].cpu().numpy().reshape(rows, cfg.width, fmt), st
 
 
