@@ -1234,9 +1234,15 @@ struct CopyJob {
         populate_range(lo, hi);
     }
 
-    void copy_slab(uint32_t s) const
+    // A slab is copied in kSlabParts parts, each claimed on its own: what stays exposed at the end of a frame is the copy of the
+    // LAST slab, and four threads finish it in a quarter of the time (C2: 768 KB, ~77 us for one thread).
+    static constexpr uint32_t kSlabParts = 4;
+    void copy_slab(uint32_t s, uint32_t part) const
     {
-        const uint32_t r0 = s * slab_rows, r1 = std::min(rows, r0 + slab_rows);
+        const uint32_t s0 = s * slab_rows, s1 = std::min(rows, s0 + slab_rows);
+        const uint32_t per = (s1 - s0 + kSlabParts - 1) / kSlabParts;
+        const uint32_t r0 = std::min(s1, s0 + part * per), r1 = std::min(s1, r0 + per);
+        if (r0 >= r1) return;
         if (!framed) {
             memcpy(dst + (size_t)r0 * row_bytes, stage + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_bytes);
             return;
@@ -1258,7 +1264,8 @@ struct CopyJob {
             populate_piece(i);
         }
         for (;;) {
-            const uint32_t s = next.fetch_add(1, std::memory_order_relaxed);
+            const uint32_t item = next.fetch_add(1, std::memory_order_relaxed);
+            const uint32_t s = item / kSlabParts;
             if (s >= nslabs) break;
             uint32_t spins = 0;
             while (done[s] == 0u) {
@@ -1272,7 +1279,7 @@ struct CopyJob {
                 }
             }
             std::atomic_thread_fence(std::memory_order_acquire);  // the slab's pixels were written before its count
-            copy_slab(s);
+            copy_slab(s, item % kSlabParts);
         }
     out:
         running.fetch_sub(1, std::memory_order_release);
