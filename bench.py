@@ -383,6 +383,8 @@ class Bench:
         st = None
         for back in range(min(ahead, n) - 1, -1, -1):
             st = harvest(back)
+        e1.synchronize()
+        torch.cuda.synchronize()
         self.barrier()
         tw1 = time.perf_counter()
         ms = self.reduce(e0.elapsed_time(e1), "max")
