@@ -251,7 +251,8 @@ uint32_t frb_fern_default_threads(void);
 /* Same as frb_render_shard but `dev_out` is DEVICE memory on `device` (>= rows*width*format bytes,
  * 16-byte aligned). `stream` is a cudaStream_t (NULL = the library's own stream for that device).
  * Returns after enqueueing; results are complete when `stream` has drained. Stats (iterations etc.)
- * are harvested by frb_sync_stats(). */
+ * are harvested by frb_sync_stats().  Renders on ONE stream run strictly in order; renders issued on two
+ * different streams use separate sets of the library's device buffers and may overlap on the device. */
 int frb_render_device_async(const FrbConfig *cfg, const FrbShard *shard, void *dev_out, size_t out_len,
                             uint32_t format, int device, void *stream);
 /* Waits for the last *_async render of this thread and fills its statistics. */
