@@ -19,8 +19,8 @@
 // (2B-1 for a pixel that ran into the iteration cap) from the record with the reference's test after every step — at full lane efficiency, ~B/2 useful iterations per
 // pixel against ~1400 in the frame — and overwrites the record with what calc::recursive returns.
 //
-// Why B+1 steps always suffice (same host-checked precondition as the sparse kernel, frb_api.cu: sparse_is_safe:
-// R = limit >= 8, |c| <= R^2/2 - 3R, S = R^2 <= 1e300): a stop by the filter means the block's last position has
+// Why B+1 steps always suffice (host-checked precondition, frb_api.cu: deferred_is_safe:
+// 8 <= R = limit <= 2^20, |c| <= R^2/2 - 3R): a stop by the filter means the block's last position has
 // max(re^2, im^2) >= S/2.  Either some step of the block escaped (an escaped orbit keeps growing to inf/NaN, which
 // also fire the unsigned filter, so no escape is ever missed at a block end), or the last step was a near miss and
 // the next one has |z| >= |z_prev|^2 - |c| >= 3R, which escapes.  A stop by the budget leaves r = iterations mod B < B

@@ -1,5 +1,5 @@
-// frb_tile.cuh — K1t: the short-orbit kernel.  One thread per pixel, warps on 8x4-pixel tiles, the escape filter after every
-// iteration, colour computed in the same kernel from the registers.  Included by frb_kernels.cuh.
+// frb_tile.cuh — K1t: the short-orbit kernel.  One thread per pixel, independent warps on 8x4-pixel (or 32x1) tiles, one escape
+// filter per pair of iterations, colour computed in the same kernel from the registers.  Included by frb_kernels.cuh.
 //
 // The lane-refill kernels (K1c and its predecessors) pay per PIXEL: a wasted half block, the idle rest of a trip, a share of a
 // service call, a 20-byte record through HBM and up to B+1 lock-step resolve steps — about 30-50 SMSP cycles, which is
