@@ -28,7 +28,7 @@ from .calc import RGB, Algo, Config, FrbConfig, Imaginary
 
 __all__ = [
     "Algo", "Config", "Imaginary", "RGB", "FrbError", "Shard", "get_image", "get_image_rgba", "get_image_into",
-    "render_shard", "render_counts", "render_frames", "render_device_async", "sync_stats", "async_stats", "last_stats",
+    "render_shard", "render_counts", "render_frames", "render_device_async", "render_static_async", "sync_stats", "async_stats", "last_stats",
     "device_count", "init", "shutdown", "render_fern", "fern_default_threads", "set_kernel_variant", "measure_fp64_peak", "shard_rows", "shard_row_to_y",
     "init_list", "set_tuning", "render_bands", "SharedFrame",
     "FRB_RGB24", "FRB_RGBA32", "pinned_empty", "KERNEL_AUTO", "KERNEL_STREAM7", "KERNEL_SIMPLE", "KERNEL_DENSE6", "KERNEL_DEFER6", "KERNEL_TILE", "KERNEL_NAMES",
@@ -256,6 +256,17 @@ def render_device_async(config: Config, dev_ptr: int, nbytes: int, fmt: int = FR
     c = config.to_c()
     s, p = _shard_ptr(shard)
     _lib.check(_lib.load().frb_render_device_async(ctypes.byref(c), p, ctypes.c_void_p(dev_ptr), nbytes, fmt, device,
+                                                   ctypes.c_void_p(stream) if stream else None))
+
+
+def render_static_async(config: Config, dev_ptr: int, nbytes: int, fmt: int = FRB_RGB24, device: int = 0, stream: int = 0) -> None:
+    """Enqueue a whole-frame render into DEVICE memory through frb_render_static_async, the entry point that allocates
+    nothing: for hosts that cannot call cudaMalloc when they need a frame (all of HBM already owned by the host's pool,
+    no device-wide stall allowed mid-loop, allocator not re-entrant where we are called).  Scratch is a fixed static
+    device array, hence frames of at most 1 048 576 pixels with width + height <= 16 384 (FrbError FRB_ERR_TOO_LARGE
+    beyond), and calls that overlap on the GPU race: keep them on one stream.  `stream` 0 = the legacy default stream."""
+    c = config.to_c()
+    _lib.check(_lib.load().frb_render_static_async(ctypes.byref(c), ctypes.c_void_p(dev_ptr), nbytes, fmt, device,
                                                    ctypes.c_void_p(stream) if stream else None))
 
 

@@ -53,6 +53,7 @@ EXPORTS = (
     "frb_render_fern",
     "frb_fern_default_threads",
     "frb_render_device_async",
+    "frb_render_static_async",
     "frb_sync_stats",
     "frb_async_stats",
     "frb_last_error",
@@ -192,6 +193,9 @@ def load() -> ctypes.CDLL:
     L.frb_render_device_async.restype = ctypes.c_int
     L.frb_render_device_async.argtypes = [P(FrbConfig), P(FrbShard), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32,
                                           ctypes.c_int, ctypes.c_void_p]
+    L.frb_render_static_async.restype = ctypes.c_int
+    L.frb_render_static_async.argtypes = [P(FrbConfig), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_int,
+                                          ctypes.c_void_p]
     L.frb_sync_stats.restype = ctypes.c_int
     L.frb_sync_stats.argtypes = [P(FrbStats)]
     L.frb_async_stats.restype = ctypes.c_int

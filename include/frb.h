@@ -261,6 +261,37 @@ int frb_sync_stats(FrbStats *stats);
  * library keeps the 32 most recent), so a caller can keep the next frame enqueued while harvesting. */
 int frb_async_stats(uint32_t back, FrbStats *stats);
 
+/* ---- render without allocating (no counterpart in the reference) ------------------------------------------------- */
+
+/* No counterpart in the reference (its get_image allocates a fresh Vec per call, src/lib.rs:266): an addition for hosts that
+ * must not, or cannot, allocate GPU memory at the moment they want a frame.  Every other render entry point grows the
+ * library's device buffers with cudaMalloc when a frame is larger than the last; that is out of the question for a plug-in
+ * inside a process whose own pool allocator has already taken all of HBM (a cudaMalloc there fails, or starves the host's
+ * next allocation), for an interactive loop that cannot afford the device-wide synchronisation cudaMalloc / cudaFree imply
+ * each time the window is resized, and for code running where the CUDA allocator must not be entered (inside another
+ * library's callback, under a lock its allocator also takes).
+ *
+ * This call renders the WHOLE frame of `cfg` into the caller's DEVICE buffer `dev_out` (on `device`, 16-byte aligned,
+ * out_len >= width*height*format) on `stream` (a cudaStream_t; NULL = the legacy default stream) and returns after
+ * enqueueing three kernels; the image is complete when `stream` has drained.  It calls no cudaMalloc, cudaFree,
+ * cudaHostAlloc, stream / event creation or other allocating routine, on any call.  Its scratch memory (coordinate tables,
+ * per-pixel count and final-z records, work counter, statistics words) is ONE file-scope `static __device__` array in
+ * csrc/frb_noalloc.cu, so:
+ *   - LIMIT: width * height <= 1 048 576 pixels and width + height <= 16 384; anything larger is refused with
+ *     FRB_ERR_TOO_LARGE and a message naming the limit (use frb_render_device_async there).  The array is 20.1 MiB; every GPU
+ *     that loads this library's code holds it until the process exits, used or not;
+ *   - the FIRST call on each device does the set-up for that device (looks up the array's device address with
+ *     cudaGetSymbolAddress while that device is current, queries occupancy, loads the kernels' code).  Make that first call
+ *     early — in particular before any stream capture is begun;
+ *   - all calls on one device share the array, and it keeps the previous call's contents (the first kernel of each call
+ *     clears the counter and statistics words, every other word is written before it is read within the call).  Two calls
+ *     whose kernels overlap on the GPU — different streams, or two host threads on unordered streams — RACE on it and both
+ *     images are garbage.  Order them: same stream, or an event between them.  Other entry points use other memory and
+ *     may run beside it.
+ * Pixels are those of frb_render_device_async, byte for byte (it runs the 7-instruction persistent kernel, exact for any
+ * input, then the same shade kernel); no statistics are harvested (frb_sync_stats does not see this call). */
+int frb_render_static_async(const FrbConfig *cfg, void *dev_out, size_t out_len, uint32_t format, int device, void *stream);
+
 /* ---- headless frame server (the reference GUI's render thread without the window) -------- */
 
 /* Mirrors src/gui.rs:37-48 (request_redraw, latest-wins coalescing through working/try_redraw), :56-82 (render thread:
