@@ -35,6 +35,7 @@ from __future__ import annotations
 import argparse
 import ctypes
 import json
+import mmap
 import os
 import statistics
 import subprocess
@@ -413,6 +414,8 @@ class Bench:
         self.barrier()
         t0 = time.perf_counter()
         iters = launches = 0
+        per_call = []
+        tc = t0
         for _ in range(n):
             call()
             s = frb.last_stats()
@@ -420,11 +423,16 @@ class Bench:
             launches += s["kernel_launches"]
             if after:
                 after()  # N > 1: the frame ends when every rank's bands are on the host
+            tn = time.perf_counter()
+            per_call.append(tn - tc)
+            tc = tn
         t1 = time.perf_counter()
         self.barrier()
         secs = self.reduce(t1 - t0, "max")
         iters_all = self.reduce(float(iters), "sum")
+        # median and min per frame beside the mean (this rank's calls; with a barrier per frame every rank sees the same)
         return {"s_total": secs, "frames": n, "reps": reps, "ms_per_frame": secs / n * 1e3, "g_iter_s": iters_all / secs / 1e9,
+                "ms_median": statistics.median(per_call) * 1e3, "ms_min": min(per_call) * 1e3,
                 "launches": launches, "window": (t0, t1)}
 
 
@@ -442,6 +450,94 @@ def run_c5(b: Bench, args, cfgs):
     steps = max(1, min(args.steps, 5))
     res = b.time_e2e(call, steps, 1, min_s=0.0, after=frame.barrier if b.world > 1 else None)
     return res, steps
+
+
+def workload_record(b: Bench, name: str, cfg, total_iterations: int, strong: bool, peak: dict, sampler) -> dict:
+    """One more configuration measured the way the headline is: device-resident (two frames in flight), the iterate kernel alone
+    (one frame at a time), and end to end — N = 1: frb_render into a malloc'd buffer per frame, a new mapping per frame and a pinned buffer; N > 1: frb_render_bands
+    per rank into one shared host frame with a barrier per frame.  >= 0.3 s per timed region."""
+    frb, np = b.frb, b.np
+    L = frb._lib.load()
+    shard = frb.Shard(b.rank, b.world, 16) if strong else frb.Shard()
+    dev = b.time_device(cfg, shard, 5, 3, min_s=0.3)
+    one = b.time_device(cfg, shard, 5, 3, min_s=0.3, pipelined=False)
+    c_cfg = cfg.to_c()
+    nbytes = cfg.width * cfg.height * 3
+    peak_tflops = peak["dfma_per_s"] * 2 / 1e12
+    flop = (total_iterations / b.world if strong else total_iterations) * FLOP_PER_ITER
+    rec = {"workload": WORKLOAD_TEXT[name], "iterations_per_frame": total_iterations, "kernel": frb.KERNEL_NAMES[dev["variant"]],
+           "device_ms": round(dev["ms_per_frame"], 4), "g_iter_s": round(dev["g_iter_s"], 1),
+           "single_stream_ms": round(one["ms_per_frame"], 4), "kernel_ms": round(one["iterate_ms"], 4), "shade_kernel_ms": round(one["shade_ms"], 4),
+           "frac": round(one["my_iters"] / one["frames"] * FLOP_PER_ITER / (one["iterate_ms"] * 1e-3) / 1e12 / peak_tflops, 4),
+           "step_frac": round(flop / (dev["ms_per_frame"] * 1e-3) / 1e12 / peak_tflops, 4),
+           "lane_utilisation": round(one["my_iters"] / one["lane_iters"], 4) if one["lane_iters"] else None}
+    if strong:
+        frame = b.shared_frame("w" + name, nbytes)
+        c_shard = shard.to_c()
+        e = b.time_e2e(lambda: frb._lib.check(L.frb_render_bands(ctypes.byref(c_cfg), ctypes.byref(c_shard), frame.array.ctypes.data, nbytes,
+                                                                    frb.FRB_RGB24, b.local)), 5, 3, min_s=0.3, after=frame.barrier)
+        rec.update({"e2e_bands_ms": round(e["ms_per_frame"], 4), "e2e_bands_ms_median": round(e["ms_median"], 4), "e2e_bands_ms_min": round(e["ms_min"], 4),
+                    "e2e_g_iter_s": round(e["g_iter_s"], 1), "partition": "one frame, interleaved 16-row bands into one shared host frame"})
+        window = e["window"]
+    else:
+        keep = []
+
+        def fresh():
+            out = np.frombuffer(mmap.mmap(-1, nbytes), dtype=np.uint8)
+            keep[:] = [out]
+            frb._lib.check(L.frb_render(ctypes.byref(c_cfg), out.ctypes.data, nbytes, frb.FRB_RGB24, b.local))
+
+        def recycled():
+            out = np.empty(nbytes, np.uint8)
+            keep[:] = [out]
+            frb._lib.check(L.frb_render(ctypes.byref(c_cfg), out.ctypes.data, nbytes, frb.FRB_RGB24, b.local))
+
+        pinned = frb.pinned_empty(nbytes)
+        er = b.time_e2e(recycled, 5, 3, min_s=0.3)
+        ef = b.time_e2e(fresh, 5, 3, min_s=0.3)
+        ep = b.time_e2e(lambda: frb._lib.check(L.frb_render(ctypes.byref(c_cfg), pinned.ctypes.data, nbytes, frb.FRB_RGB24, b.local)), 5, 3, min_s=0.3)
+        # e2e_ms: malloc per frame (the drop-in's steady state: recycled resident blocks; "e2e_fresh_ms" of rounds 1-2);
+        # e2e_fresh_map_ms: a new anonymous mapping per frame; e2e_pinned_ms: a reused page-locked buffer
+        rec.update({"e2e_ms": round(er["ms_per_frame"], 4), "e2e_ms_median": round(er["ms_median"], 4), "e2e_ms_min": round(er["ms_min"], 4),
+                    "e2e_fresh_map_ms": round(ef["ms_per_frame"], 4), "e2e_fresh_map_ms_median": round(ef["ms_median"], 4), "e2e_fresh_map_ms_min": round(ef["ms_min"], 4),
+                    "e2e_pinned_ms": round(ep["ms_per_frame"], 4), "e2e_pinned_ms_median": round(ep["ms_median"], 4), "e2e_pinned_ms_min": round(ep["ms_min"], 4),
+                    "e2e_g_iter_s": round(er["g_iter_s"], 1)})
+        window = er["window"]
+    if b.rank == 0:
+        rec["clocks"] = sampler.window(*window)
+    return rec
+
+
+def c5_record(b: Bench, cfgs, sampler) -> dict:
+    """C5 in the headline line: the 240-frame zoom through frb_render_frames_strided, frames k % N == rank per rank, every frame into its
+    place in one shared host buffer, a barrier per animation; >= 3 animations.  N > 1: rank 0 also runs the whole animation alone
+    (this run's N = 1 denominator)."""
+    frb = b.frb
+    fbytes = cfgs[0].width * cfgs[0].height * 3
+    frame = b.shared_frame("x5", fbytes * len(cfgs))
+
+    def call():
+        frb.render_frames(cfgs, frb.FRB_RGB24, device=b.local, out=frame.array, first=b.rank, stride=b.world)
+
+    res = b.time_e2e(call, 3, 1, min_s=0.0, after=frame.barrier if b.world > 1 else None)
+    rec = {"workload": WORKLOAD_TEXT["C5"], "frames": len(cfgs), "animations_timed": res["frames"],
+           "ms_per_animation": round(res["ms_per_frame"], 2), "ms_median": round(res["ms_median"], 2), "ms_min": round(res["ms_min"], 2),
+           "frames_per_s": round(len(cfgs) * res["frames"] / res["s_total"], 1), "g_iter_s": round(res["g_iter_s"], 1),
+           "frames_per_gpu": [len(range(r, len(cfgs), b.world)) for r in range(b.world)],
+           "api": "frb_render_frames_strided per rank (two frames in flight per GPU), each frame copied to its place in ONE shared pinned host buffer"}
+    if b.rank == 0:
+        rec["clocks"] = sampler.window(*res["window"])
+    if b.world > 1:
+        if b.rank == 0:
+            t = []
+            for _ in range(2):
+                t0 = time.perf_counter()
+                frb.render_frames(cfgs, frb.FRB_RGB24, device=b.local, out=frame.array)
+                t.append((time.perf_counter() - t0) * 1e3)
+            rec["n1_ms_per_animation_same_run"] = round(min(t), 2)
+            rec["efficiency"] = round(min(t) / (b.world * res["ms_per_frame"]), 4)
+        frame.barrier()
+    return rec
 
 
 def main():
@@ -503,7 +599,7 @@ def main():
     c_cfg = cfg.to_c()
     L = frb._lib.load()
     full_bytes = cfg.width * cfg.height * 3
-    e2e_pinned = None
+    e2e_pinned = e2e_fresh_map = None
     if strong:
         frame = b.shared_frame("main", full_bytes)
         c_shard = shard.to_c()
@@ -520,7 +616,16 @@ def main():
         keep = []
 
         def call_fresh():
-            # what rust/ffi.rs get_image_b200 does: a fresh, untouched allocation per frame (Vec::with_capacity), frb_render into it
+            # A destination NO ONE has touched: an anonymous mapping of its own per frame (what malloc hands a Rust
+            # Vec::with_capacity of this size the first time, or whenever the caller keeps the previous frames alive); it is
+            # unmapped when the next frame replaces it.  np.empty would not do: after the first free glibc raises its mmap
+            # threshold (up to 32 MB) and serves the same two, already resident, heap blocks from then on.
+            out = np.frombuffer(mmap.mmap(-1, full_bytes), dtype=np.uint8)
+            keep[:] = [out]
+            frb._lib.check(L.frb_render(ctypes.byref(c_cfg), out.ctypes.data, full_bytes, frb.FRB_RGB24, local))
+
+        def call_recycled():
+            # what a caller that drops its Vec every frame gets from glibc after the first few frames: pageable, but resident
             out = np.empty(full_bytes, np.uint8)
             keep[:] = [out]
             frb._lib.check(L.frb_render(ctypes.byref(c_cfg), out.ctypes.data, full_bytes, frb.FRB_RGB24, local))
@@ -530,10 +635,14 @@ def main():
         def call_pinned():
             frb._lib.check(L.frb_render(ctypes.byref(c_cfg), pinned.ctypes.data, full_bytes, frb.FRB_RGB24, local))
 
-        e2e = b.time_e2e(call_fresh, args.steps, args.warmup)
+        e2e = b.time_e2e(call_recycled, args.steps, args.warmup)
+        e2e_fresh_map = b.time_e2e(call_fresh, args.steps, args.warmup, min_s=0.5)
         e2e_pinned = b.time_e2e(call_pinned, args.steps, args.warmup)
-        e2e_api = ("frb_render(cfg, out, len, RGB24, device) into a FRESH pageable allocation per frame (np.empty = Vec::with_capacity, as "
-                   "rust/ffi.rs get_image_b200 does; allocation and first-touch page faults inside the timed region); weak N > 1: one such frame per rank")
+        e2e_api = ("frb_render(cfg, out, len, RGB24, device) into a pageable buffer allocated per frame with malloc (np.empty = Vec::with_capacity, as "
+                   "rust/ffi.rs get_image_b200 does) and dropped when the next frame arrives: after the first frames glibc serves these allocations "
+                   "from the same resident heap blocks (its mmap threshold rises on the first free), so this is the steady state of the drop-in, NOT "
+                   "untouched memory — rounds 1-2 called this arm 'fresh'; the cost of a destination nobody has touched (a new anonymous mapping "
+                   "per frame: the first call of a process, or a caller that keeps every frame) is e2e_fresh_map; weak N > 1: one such frame per rank")
         d2h = full_bytes
 
     # ---------------- extras: evidence the driver can only get from this run ----------------
@@ -549,7 +658,8 @@ def main():
                 n1_e2e = b.time_e2e(lambda: frb._lib.check(L.frb_render(ctypes.byref(c_cfg), pin1.ctypes.data, full_bytes, frb.FRB_RGB24, local)),
                                     max(5, args.steps // 2), 3, min_s=0.5)
                 b.dist = saved
-                extra["n1_same_run"] = {"ms_per_frame": round(n1_dev["ms_per_frame"], 4), "g_iter_s": round(n1_dev["g_iter_s"], 1),
+                extra["n1_same_run"] = {"arm": "two frames in flight on two streams, the same arm as `value`",
+                                        "ms_per_frame": round(n1_dev["ms_per_frame"], 4), "g_iter_s": round(n1_dev["g_iter_s"], 1),
                                         "e2e_pinned_ms_per_frame": round(n1_e2e["ms_per_frame"], 4)}
                 extra["strong_efficiency"] = {"device_resident": round(n1_dev["ms_per_frame"] / (world * dev["ms_per_frame"]), 4),
                                               "e2e": round(n1_e2e["ms_per_frame"] / (world * e2e["ms_per_frame"]), 4),
@@ -566,9 +676,11 @@ def main():
         def call_c4():
             frb._lib.check(L.frb_render_bands(ctypes.byref(c4_c), ctypes.byref(c4_s), c4_frame.array.ctypes.data, c4_bytes, frb.FRB_RGB24, local))
 
-        c4_res = b.time_e2e(call_c4, 3, 1, min_s=0.0, after=c4_frame.barrier if world > 1 else None)
+        c4_res = b.time_e2e(call_c4, 5, 1, min_s=1.0, after=c4_frame.barrier if world > 1 else None)
         rec = {"workload": WORKLOAD_TEXT["C4"], "partition": "one frame, interleaved 16-row bands" if world > 1 else "single GPU",
-               "ms_per_frame": round(c4_res["ms_per_frame"], 3), "g_iter_s": round(c4_res["g_iter_s"], 1), "frames_timed": c4_res["frames"],
+               "ms_per_frame": round(c4_res["ms_per_frame"], 3), "ms_median": round(c4_res["ms_median"], 3), "ms_min": round(c4_res["ms_min"], 3),
+               "g_iter_s": round(c4_res["g_iter_s"], 1), "frames_timed": c4_res["frames"], "timed_region_s": round(c4_res["s_total"], 3),
+               "clocks": sampler.window(*c4_res["window"]) if rank == 0 else None,
                "measured": "end to end: frb_render_bands per rank into one shared pinned host frame + barrier per frame (gather to host included)"}
         if world > 1:
             n1 = None
@@ -624,6 +736,28 @@ def main():
                 extra["shared_frame_check"] = "ok" if np.array_equal(frame.array[:full_bytes], one) else "MISMATCH"
             frame.barrier()
 
+    # (4) the other configurations of BASELINE.json in the same driver-run line: C1 and C3 (device-resident, kernel, end to end; at
+    # N > 1 the same band partition into a shared host frame) and C5 (the zoom animation sharded by frame, examples.md:20-29)
+    if not args.no_extras and args.workload in ("C2", "C2b"):
+        extra["workloads"] = {}
+        for wname in ("C1", "C3"):
+            try:
+                rec = workload_record(b, wname, configs.BY_NAME[wname](), configs.TOTAL_ITERATIONS[wname], strong, peak, sampler)
+            except Exception as e:  # evidence, not a reason to lose the headline line — but only where no other rank waits on a barrier
+                if world > 1:
+                    raise
+                rec = f"FAILED: {e}"
+            if rank == 0:
+                extra["workloads"][wname] = rec
+        try:
+            rec = c5_record(b, configs.c5(), sampler)
+        except Exception as e:
+            if world > 1:
+                raise
+            rec = f"FAILED: {e}"
+        if rank == 0:
+            extra["c5"] = rec
+
     if rank != 0:
         b.close()
         return
@@ -668,7 +802,9 @@ def main():
         "kernel_share_of_step": round(it_ms / one_stream["ms_per_frame"], 4),
         "kernel_ms_note": "CUDA events around the iterate kernel alone, frames issued one at a time on one stream (extra.single_stream); "
                           "step_frac is over the headline arm (two frames in flight)",
-        "peak_source": "measured in this run: frb_measure_fp64_peak DFMA stream x 2 flop (MEASURED_PEAKS.json has no FP64 entry)",
+        "peak_source": "measured in this run: frb_measure_fp64_peak DFMA stream x 2 flop (MEASURED_PEAKS.json has no FP64 entry; the same "
+                       "measurement with its clock sample is kept in profiles/r3_fp64_peak.json)",
+        "peak_sm_clock_mhz": round(peak.get("sm_clock_mhz", 0.0), 1),
         "peak_nominal": FP64_NOMINAL_TFLOPS, "frac_of_nominal": round(achieved_tflops / FP64_NOMINAL_TFLOPS, 4),
         "fp64_instr_per_iter": form,
         "pipe_frac": round(per_launch_iters * form / (it_ms * 1e-3) / peak["dfma_per_s"], 4),
@@ -693,25 +829,36 @@ def main():
         "metric": "G iter/s", "value": round(dev["g_iter_s"], 2), "unit": "G iter/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": round(dev["ms_total"] / args.steps, 4), "higher_is_better": True, "scaling": "strong" if strong else "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic (the fractal itself: deterministic, no RNG, no dataset)",
-        "config": {
-            "workload": WORKLOAD_TEXT[args.workload], "iterations_per_frame": total_iterations, "frames_per_step": frames_per_step,
+        "config": {"workload": WORKLOAD_TEXT[args.workload], "iterations_per_frame": total_iterations},  # the same two keys as --impl reference
+        "run": {
+            "frames_per_step": frames_per_step,
             "timed_region_s": round(dev["ms_total"] * 1e-3, 3),
             "partition": ("one frame, interleaved 16-row bands" if strong else "one whole frame per rank") if world > 1 else "single GPU",
             "kernel": frb.KERNEL_NAMES[kv], "format": "RGB24",
             "issue": "device-resident arm: independent frames on two streams, two in flight per GPU (the next frame's CTAs fill the SMs the "
-                     "previous frame has left, as frb_render_frames does); e2e arm: one blocking call at a time",
+                     "previous frame has left, as frb_render_frames does); e2e arm: one blocking call at a time"
+                     + ("; at N > 1 `value` leaves every rank's bands in its own HBM and gathers nothing: the partition's number, with the "
+                        "whole image on the host, is `e2e`" if world > 1 else ""),
             "l2": "not flushed: no reusable input (%d KB of coordinate tables are recomputed every frame); each frame writes %.0f MB of new data (%s)" % (
                 (cfg.width + cfg.height) * 8 // 1024, cfg.width * cfg.height * (3 if kv == frb.KERNEL_TILE else 23) / 1e6,
                 "3 B/px image; smaller than the 126 MB L2, nothing is read back" if kv == frb.KERNEL_TILE else "20 B/px provisional records + 3 B/px image"),
         },
         "ms_per_frame": round(dev["ms_per_frame"], 4),
         "e2e": {"value": round(e2e["g_iter_s"], 2), "unit": "G iter/s", "h2d_bytes_per_step": 104 * e2e["reps"], "d2h_bytes_per_step": (d2h + 16 * (world if strong else 1)) * e2e["reps"],
-                "ms_per_frame": round(e2e["ms_per_frame"], 4), "frames_per_step": e2e["reps"], "timed_region_s": round(e2e["s_total"], 3), "api": e2e_api},
+                "ms_per_frame": round(e2e["ms_per_frame"], 4), "ms_median": round(e2e["ms_median"], 4), "ms_min": round(e2e["ms_min"], 4),
+                "frames_per_step": e2e["reps"], "timed_region_s": round(e2e["s_total"], 3), "api": e2e_api},
         "gpu_launches": dev["launches"] + one_stream["launches"] + e2e["launches"],
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "extra": extra,
     }
     if e2e_pinned is not None:
+        line["e2e_fresh_map"] = {"value": round(e2e_fresh_map["g_iter_s"], 2), "unit": "G iter/s", "ms_per_frame": round(e2e_fresh_map["ms_per_frame"], 4),
+                                 "ms_median": round(e2e_fresh_map["ms_median"], 4), "ms_min": round(e2e_fresh_map["ms_min"], 4),
+                                 "api": "the same frb_render call into a NEW anonymous mapping per frame (mmap and the previous frame's munmap inside the "
+                                        "timed region): every page of the destination is first-touched during the frame — ~0.2 ms per MB of kernel page "
+                                        "faults on this box, which the staging pipeline hides only as far as the iterations last"}
+        line["gpu_launches"] += e2e_fresh_map["launches"]
         line["e2e_pinned"] = {"value": round(e2e_pinned["g_iter_s"], 2), "unit": "G iter/s", "ms_per_frame": round(e2e_pinned["ms_per_frame"], 4),
+                              "ms_median": round(e2e_pinned["ms_median"], 4), "ms_min": round(e2e_pinned["ms_min"], 4),
                               "api": "the same frb_render call into a reused page-locked buffer (frb_host_alloc): written by the streaming finisher over PCIe while the iterate kernel runs"}
         line["gpu_launches"] += e2e_pinned["launches"]
     print(json.dumps(line), flush=True)

@@ -1092,6 +1092,16 @@ double now_ms()
 // framed = false: `host_out` receives the shard's own compact image (its rows in increasing y).
 // framed = true:  `host_out` is the WHOLE frame and the shard's bands go to their place in it (band b of the shard starts at
 //                 ((b * count + index) * band_rows) rows) — how several devices, or several processes, assemble one image.
+// Error paths: work already launched may still write into a staging buffer (image or flags) or the caller's memory.  Wait for
+// the device's three streams — ignoring what they report, the caller already has its error — before that memory changes hands.
+void drain_streams(DeviceCtx &c)
+{
+    cudaStreamSynchronize(c.stream);
+    cudaStreamSynchronize(c.aux[0]);
+    cudaStreamSynchronize(c.aux[1]);
+    cudaGetLastError();
+}
+
 int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t format, uint8_t *host_out, size_t out_len,
                     uint32_t *host_iters, double *host_z, bool framed = false)
 {
@@ -1169,6 +1179,7 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
         int rc = enqueue_streamed(*c, plan, sb->p, c->stream, &slot, sb->done);
         if (!rc) rc = finish_enqueue(*c, *slot, c->stream);
         if (rc) {
+            drain_streams(*c);  // the finisher / the kernels launched before the failing call may still be writing
             g_stage.release(sb);
             return rc;
         }
@@ -1250,6 +1261,7 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
         int rc = enqueue(*c, plan, tile_stage->p, c->stream, &slot);
         if (!rc) rc = finish_enqueue(*c, *slot, c->stream);
         if (rc) {
+            drain_streams(*c);  // the finisher / the kernels launched before the failing call may still be writing
             g_stage.release(tile_stage);
             return rc;
         }
@@ -1294,12 +1306,19 @@ int render_blocking(const FrbConfig &cfg, const FrbShard &sh, int dev, uint32_t 
             job->plan_populate();
             int rc = enqueue_sliced(*c, plan, sb2->p, nslabs, &slot, 0, sb2->done);
             if (rc) {
+                drain_streams(*c);  // slab copies and host functions queued before the failing call
                 g_stage.release(sb2);
                 return rc;
             }
             g_copy.post(job, helpers);
-            job->run();  // the flags are raised in stream order: the rendering thread copies along
+            job->run(c->stream);  // the flags are raised in stream order: the rendering thread copies along, and watches the stream
             job->wait_idle();
+            if (job->abort.load()) {
+                const cudaError_t we = job->watch_error;
+                drain_streams(*c);
+                g_stage.release(sb2);
+                return fail(FRB_ERR_CUDA, "sliced render abandoned: %s", cudaGetErrorString(we));
+            }
             g_stage.release(sb2);
         } else if (int rc = enqueue_sliced(*c, plan, dst0, nslabs, &slot, band_pitch)) {
             return rc;
@@ -1773,13 +1792,8 @@ int frb_render(const FrbConfig *cfg, uint8_t *out, size_t out_len, uint32_t form
         if (parts[g].rc != FRB_OK) parts[g].err = tl_error;
         else parts[g].stats = tl_stats;
     };
-    std::vector<DeviceWorker *> workers(G, nullptr);
-    for (uint32_t g = 1; g < G; ++g) {
-        workers[g] = get_worker(g);  // one worker per SHARD slot: a device listed twice gets two (they serialise on its mutex)
-        workers[g]->submit([&run_part, g] { run_part(g); });
-    }
-    run_part(0);
-    for (uint32_t g = 1; g < G; ++g) workers[g]->wait();
+    // one worker per SHARD slot: a device listed twice gets two (they serialise on its mutex)
+    run_parts_on_workers(G, run_part);
     FrbStats total = {};
     for (uint32_t g = 0; g < G; ++g) {
         if (parts[g].rc != FRB_OK) return fail(parts[g].rc, "device %d: %s", devs[g], parts[g].err.c_str());
@@ -1900,13 +1914,19 @@ int frb_render_frames_strided(const FrbConfig *cfgs, uint32_t n, uint8_t *out, s
                     rc = fail(FRB_ERR_CUDA, "cudaMemcpyAsync (frame %u) failed: %s", k, cudaGetErrorString(cudaGetLastError()));
                 if (!rc) rc = finish_enqueue(c, *slot, st);
                 c.cur_set = 0;
-                if (rc) return rc;
+                if (rc) {
+                    drain_streams(c);  // up to two frames' copies into the caller's `out` are still in flight
+                    return rc;
+                }
                 pending[npending].slot = slot;
                 pending[npending].done = slot->ev_end;
                 ++npending;
             }
             if (npending == 0) break;
-            if (int rc = retire_oldest()) return rc;
+            if (int rc = retire_oldest()) {
+                drain_streams(c);
+                return rc;
+            }
         }
         return FRB_OK;
     };
@@ -1918,13 +1938,7 @@ int frb_render_frames_strided(const FrbConfig *cfgs, uint32_t n, uint8_t *out, s
             failed.store(true);
         }
     };
-    std::vector<DeviceWorker *> workers(G, nullptr);
-    for (uint32_t g = 1; g < G; ++g) {
-        workers[g] = get_worker(g);
-        workers[g]->submit([&run_part, g] { run_part(g); });
-    }
-    run_part(0);
-    for (uint32_t g = 1; g < G; ++g) workers[g]->wait();
+    run_parts_on_workers(G, run_part);
     FrbStats total = {};
     for (uint32_t g = 0; g < G; ++g) {
         if (parts[g].rc != FRB_OK) return fail(parts[g].rc, "device %d: %s", devs[g], parts[g].err.c_str());

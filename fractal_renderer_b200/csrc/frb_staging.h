@@ -30,15 +30,18 @@ public:
         for (StageBuf *b : bufs_)
             if (!b->busy && b->cap >= bytes && (!best || b->cap < best->cap)) best = b;
         if (!best) {
-            // replace the largest idle buffer that is too small rather than hoarding: at most 4 buffers are kept
+            // replace the SMALLEST idle buffer (every idle one is too small for this frame; the smallest is the least likely to
+            // fit the next) rather than hoarding: at most 4 buffers are kept.  cudaFreeHost waits for the devices' work in
+            // flight — this only happens when a process moves to a larger frame size for good.
             if (bufs_.size() >= 4) {
+                size_t victim = bufs_.size();
                 for (size_t i = 0; i < bufs_.size(); ++i)
-                    if (!bufs_[i]->busy) {
-                        cudaFreeHost(bufs_[i]->p);
-                        delete bufs_[i];
-                        bufs_.erase(bufs_.begin() + (long)i);
-                        break;
-                    }
+                    if (!bufs_[i]->busy && (victim == bufs_.size() || bufs_[i]->cap < bufs_[victim]->cap)) victim = i;
+                if (victim != bufs_.size()) {
+                    cudaFreeHost(bufs_[victim]->p);
+                    delete bufs_[victim];
+                    bufs_.erase(bufs_.begin() + (long)victim);
+                }
             }
             const size_t cap = bytes + bytes / 8 + (1u << 20);
             const size_t total = ((cap + 255) & ~(size_t)255) + kMaxStageSlabs * sizeof(uint32_t);
@@ -172,7 +175,13 @@ struct CopyJob {
         }
     }
     // Claims slabs until none is left (or the frame was abandoned).  Every participant was counted in `running` beforehand.
-    void run()
+    // `watch` (the rendering thread only): the stream whose completion implies every flag has been raised.  The flags of the
+    // sliced path come from host functions in stream order, and CUDA does not run those once the stream or the context is in an
+    // error state (a kernel fault, a failed copy) — without a look at the stream every participant would spin for ever, the
+    // rendering thread with the device's mutex held.  So while it waits, the watcher polls the stream now and then: an error, or
+    // a drained stream with the flag still down, abandons the frame (watch_error says why).
+    cudaError_t watch_error = cudaSuccess;
+    void run(cudaStream_t watch = nullptr)
     {
         for (;;) {
             const uint32_t i = next_piece.load(std::memory_order_relaxed) < npieces ? next_piece.fetch_add(1, std::memory_order_relaxed) : npieces;
@@ -192,6 +201,13 @@ struct CopyJob {
 #endif
                 } else {
                     std::this_thread::yield();
+                    if (watch != nullptr && (spins & 63u) == 0u) {
+                        const cudaError_t q = cudaStreamQuery(watch);
+                        if (q != cudaErrorNotReady && done[s] == 0u) {
+                            watch_error = q != cudaSuccess ? q : cudaErrorUnknown;  // drained, yet the callback never ran
+                            abort.store(true);
+                        }
+                    }
                 }
             }
             std::atomic_thread_fence(std::memory_order_acquire);  // the slab's pixels were written before its count

@@ -51,7 +51,8 @@ struct DeviceWorker {
             cv.notify_all();
         }
     }
-    // one job at a time per worker; the previous one has been waited for (frb_render joins every worker before it returns)
+    // one job at a time per worker, from one submitter at a time: callers hold g_dispatch_mu (run_parts_on_workers) from their
+    // first submit to their last wait, so the previous job has been waited for by whoever posted it
     void submit(std::function<void()> j)
     {
         wait();
@@ -85,6 +86,36 @@ DeviceWorker *get_worker(int dev)
         g_workers[dev] = w;
     }
     return g_workers[dev];
+}
+
+// Runs part(0) on the calling thread and part(1) .. part(G-1) on host threads of their own, and returns when all are done.
+// The persistent workers take ONE job at a time and a DeviceWorker has no notion of whose job it runs, so the set of them
+// belongs to one multi-device call at a time (g_dispatch_mu, held from the first submit to the last wait): two threads inside
+// frb_render(device = -1) / frb_render_frames at once — the GUI's render thread and its screenshot thread, src/gui.rs:60 and
+// :325 — used to overwrite each other's `job`, and the loser returned FRB_OK with its bands never rendered.  A caller that
+// finds the workers taken does not queue behind them (that could be a whole animation): it starts plain threads for this one
+// call (~50 us each), whose shards then interleave with the other call's on the devices' own mutexes, frame by frame.
+std::mutex g_dispatch_mu;
+
+template <typename Part>
+void run_parts_on_workers(uint32_t G, Part &part)
+{
+    std::unique_lock<std::mutex> pool(g_dispatch_mu, std::try_to_lock);
+    if (pool.owns_lock()) {
+        std::vector<DeviceWorker *> workers(G, nullptr);
+        for (uint32_t g = 1; g < G; ++g) {
+            workers[g] = get_worker((int)g);
+            workers[g]->submit([&part, g] { part(g); });
+        }
+        part(0);
+        for (uint32_t g = 1; g < G; ++g) workers[g]->wait();
+        return;
+    }
+    std::vector<std::thread> own;
+    own.reserve(G);
+    for (uint32_t g = 1; g < G; ++g) own.emplace_back([&part, g] { part(g); });
+    part(0);
+    for (std::thread &t : own) t.join();
 }
 
 void stop_workers_locked()

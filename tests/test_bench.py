@@ -26,6 +26,7 @@ def test_reference_arm_line():
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
     assert d["e2e"]["value"] == d["value"] and d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
     assert "workload" in d["config"] and "model" not in d["config"]
+    assert set(d["config"]) == {"workload", "iterations_per_frame"}   # the GPU arm's line carries exactly these two keys as well
 
 
 @pytest.mark.gpu
@@ -33,6 +34,8 @@ def test_gpu_arm_line():
     d = run_bench("--workload", "C1", "--steps", "2", "--warmup", "3", "--no-cpu-baseline", "--no-extras")
     assert BASE_KEYS | {"roofline", "clocks", "gpu_launches", "cpu_baseline"} <= set(d)
     assert d["n_gpus"] == 1 and d["dtype"] == "f64" and d["gpu_launches"] > 0 and d["value"] > 100
+    assert set(d["config"]) == {"workload", "iterations_per_frame"} and "kernel" in d["run"]   # same config keys as the reference arm
+    assert d["e2e"]["ms_min"] <= d["e2e"]["ms_median"] and d["e2e_fresh_map"]["value"] > 0 and d["e2e_pinned"]["value"] > 0
     r = d["roofline"]
     assert r["bound"] == "fp64" and 0.05 < r["frac"] < 0.84 and r["peak"] > 30 and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-3
     assert r["traffic"] is None or r["traffic"] >= 0

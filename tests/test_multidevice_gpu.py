@@ -89,6 +89,52 @@ def test_render_bands_assembles_one_frame_shard_by_shard(gpu):
                     assert np.array_equal(buf, ref), (name, fmt, pinned, count, band)
 
 
+def test_two_threads_in_device_minus_one_renders_at_once(gpu):
+    """The GUI's render thread and its screenshot thread (src/gui.rs:60, :325) may both be inside get_image on all devices.  The
+    per-device workers take one job from one caller at a time: the second caller must neither overwrite the first one's job nor
+    return with bands unrendered (it runs its shards on threads of its own).  One device listed three times on a 1-GPU box."""
+    import threading
+
+    scenes = [CASES["C2_ragged_height"], CASES["C3_julia"], CASES["C1_tile"], CASES["tiny"]]
+    refs = [frb.render_shard(c, frb.Shard(), frb.FRB_RGB24).reshape(-1).copy() for c in scenes]
+    frb.init_list([0, 0, 0])
+    errors = []
+
+    def caller(tid, rounds):
+        try:
+            for r in range(rounds):
+                k = (tid + r) % len(scenes)
+                cfg = scenes[k]
+                buf = np.full(cfg.width * cfg.height * 3, 0x5A, np.uint8)
+                frb.get_image_into(cfg, buf, frb.FRB_RGB24, device=-1)
+                if not np.array_equal(buf, refs[k]):
+                    errors.append(f"thread {tid} round {r} scene {k}: {np.count_nonzero(buf != refs[k])} bytes differ")
+        except Exception as e:  # noqa: BLE001 - reported below
+            errors.append(f"thread {tid}: {e!r}")
+
+    def animation():
+        try:
+            frames = [scenes[3]] * 40
+            out = frb.render_frames(frames, frb.FRB_RGB24, device=-1)
+            n = refs[3].size
+            for j in range(len(frames)):
+                if not np.array_equal(out[j * n:(j + 1) * n], refs[3]):
+                    errors.append(f"animation frame {j} differs")
+        except Exception as e:  # noqa: BLE001
+            errors.append(f"animation: {e!r}")
+
+    try:
+        threads = [threading.Thread(target=caller, args=(t, 12)) for t in range(3)] + [threading.Thread(target=animation)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join(timeout=300)
+            assert not t.is_alive(), "a concurrent device = -1 render hung"
+        assert not errors, errors[:5]
+    finally:
+        frb.init(0)
+
+
 def test_real_devices_tile_to_the_single_device_image(gpu):
     if frb.device_count() < 2:
         pytest.skip("one device visible: the real multi-device run happens in bench.py's pre-flight at N > 1 and in scripts/inprocess_scale.py")
