@@ -51,7 +51,18 @@ struct Frame {
     uint32_t ranks = 1, rank = 0;
     uint32_t local_sense = 0;
     bool pinned = false;
+    int fd = -1;  // ranks != 0 keep the file open: fstat tells whether the frame they mapped is still the one the name refers to
 };
+
+// True when the file behind `fd` has been unlinked, or `path` now names another file: a rank that attached to the left-over frame
+// of a crashed job just before this job's rank 0 removed it would otherwise render into memory nobody reads.
+bool is_stale(int fd, const std::string &path)
+{
+    struct stat mine, named;
+    if (fd < 0 || fstat(fd, &mine) != 0) return false;
+    if (mine.st_nlink == 0) return true;
+    return stat(path.c_str(), &named) == 0 && (named.st_ino != mine.st_ino || named.st_dev != mine.st_dev);
+}
 
 void cpu_relax()
 {
@@ -121,17 +132,23 @@ FrbSharedFrame *frb_shared_frame_open(const char *name, size_t bytes, uint32_t r
         }
     }
     void *m = mmap(nullptr, map_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
-    close(fd);
+    if (rank == 0) {
+        close(fd);
+        fd = -1;
+    }
     if (m == MAP_FAILED) {
         frb_internal_fail(FRB_ERR_INVALID, "mmap(%s, %zu): %s", name, map_bytes, strerror(errno));
         if (rank == 0) unlink(path.c_str());
+        if (fd >= 0) close(fd);
         return nullptr;
     }
     Frame *f = new (std::nothrow) Frame();
     if (!f) {
         munmap(m, map_bytes);
+        if (fd >= 0) close(fd);
         return nullptr;
     }
+    f->fd = fd;
     f->name = path;
     f->hdr = static_cast<Header *>(m);
     f->data = static_cast<uint8_t *>(m) + kHeaderBytes;
@@ -149,15 +166,30 @@ FrbSharedFrame *frb_shared_frame_open(const char *name, size_t bytes, uint32_t r
             if (std::chrono::steady_clock::now() - t0 > std::chrono::seconds(30)) {
                 frb_internal_fail(FRB_ERR_INVALID, "shared frame %s was never initialised by rank 0", name);
                 munmap(m, map_bytes);
+                close(f->fd);
                 delete f;
                 return nullptr;
             }
             std::this_thread::sleep_for(std::chrono::milliseconds(1));
         }
+        // The magic may be that of a crashed job's frame under the same name, opened before this job's rank 0 got to remove it:
+        // if the name has moved on, attach again (to the new file).  The barrier re-checks (a removal that comes later still).
+        static thread_local int reattach = 0;
+        if (is_stale(f->fd, path) && reattach < 100) {
+            munmap(m, map_bytes);
+            close(f->fd);
+            delete f;
+            std::this_thread::sleep_for(std::chrono::milliseconds(10));
+            ++reattach;
+            FrbSharedFrame *again = frb_shared_frame_open(name, bytes, ranks, rank);
+            --reattach;
+            return again;
+        }
         if (f->hdr->bytes != bytes || f->hdr->ranks != ranks) {
             frb_internal_fail(FRB_ERR_INVALID, "shared frame %s is %llu bytes for %u ranks, not %zu for %u", name,
                               (unsigned long long)f->hdr->bytes, f->hdr->ranks, bytes, ranks);
             munmap(m, map_bytes);
+            close(f->fd);
             delete f;
             return nullptr;
         }
@@ -203,8 +235,13 @@ int frb_shared_frame_barrier(FrbSharedFrame *h)
             cpu_relax();
         } else {
             std::this_thread::yield();
-            if ((spins & 1023u) == 0 && std::chrono::steady_clock::now() - t0 > std::chrono::seconds(60))
-                return frb_internal_fail(FRB_ERR_INVALID, "shared frame barrier: rank %u waited 60 s for the others", f->rank);
+            if ((spins & 1023u) == 0) {
+                if (is_stale(f->fd, f->name))
+                    return frb_internal_fail(FRB_ERR_INVALID, "shared frame %s: rank %u is attached to a frame that has been removed or replaced "
+                                             "(left over from another job, or rank 0 has closed it); open it again", f->name.c_str(), f->rank);
+                if (std::chrono::steady_clock::now() - t0 > std::chrono::seconds(60))
+                    return frb_internal_fail(FRB_ERR_INVALID, "shared frame barrier: rank %u waited 60 s for the others", f->rank);
+            }
         }
     }
     return FRB_OK;
@@ -216,6 +253,7 @@ void frb_shared_frame_close(FrbSharedFrame *h)
     if (!f) return;
     if (f->pinned && cudaHostUnregister(f->data) != cudaSuccess) cudaGetLastError();
     if (f->rank == 0) unlink(f->name.c_str());  // the mappings of the other ranks stay valid until they unmap
+    if (f->fd >= 0) close(f->fd);
     munmap(f->hdr, f->map_bytes);
     delete f;
 }

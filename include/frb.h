@@ -352,7 +352,10 @@ uint8_t *frb_shared_frame_data(FrbSharedFrame *frame);
 /* 1 if the mapping is page-locked (a GPU can write it directly). */
 int frb_shared_frame_pinned(FrbSharedFrame *frame);
 /* Returns when all `ranks` processes have called it the same number of times (sense-reversing counter in the shared header;
- * spins, then yields): "the whole frame is on the host".  FRB_ERR_INVALID after ~60 s without the others. */
+ * spins, then yields): "the whole frame is on the host".  FRB_ERR_INVALID after ~60 s without the others, or at once when this
+ * rank's mapping turns out to be a removed or replaced file (a crashed job's left-over under the same name).  It is ONE phase:
+ * a rank that returns may start the next frame's writes at once, so a consumer that reads frame k in place while the ranks go
+ * on needs a second barrier call after its read (or double-buffers with two frames). */
 int frb_shared_frame_barrier(FrbSharedFrame *frame);
 /* Unpins and unmaps; rank 0 also removes the name. */
 void frb_shared_frame_close(FrbSharedFrame *frame);

@@ -4,6 +4,7 @@ import os
 import sys
 
 import numpy as np
+import pytest
 import torch.multiprocessing as mp
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -104,6 +105,34 @@ def test_shared_frame_two_processes_assemble_one_image():
     assert all(g[2] for g in got if g[0] == "shared_ok") and sum(g[0] == "shared_ok" for g in got) == 3
     assert all(g[2] == 200 for g in got if g[0] == "count")
     assert not os.path.exists("/dev/shm" + name)
+
+
+def test_shared_frame_left_over_from_a_crashed_job_is_detected():
+    """A rank that attaches to the left-over frame of a crashed job (same name, magic still set) before this job's rank 0 has
+    replaced it must not sit in the barrier for a minute, let alone render into memory nobody reads: the barrier notices that
+    the file it mapped was removed and says so; a second open attaches to the new frame."""
+    import time
+    import fractal_renderer_b200 as frb
+
+    name = f"/frb-stale-{os.getpid()}"
+    crashed = frb.SharedFrame(name, 4096, 2, 0)           # the "crashed" job's rank 0: never closed, its file stays
+    late = frb.SharedFrame(name, 4096, 2, 1)              # this job's rank 1 finds the old file first
+    fresh = frb.SharedFrame(name, 4096, 2, 0)             # this job's rank 0 removes it and creates the frame anew
+    try:
+        t0 = time.perf_counter()
+        with pytest.raises(frb.FrbError) as e:
+            late.barrier()
+        assert time.perf_counter() - t0 < 20.0
+        assert "removed or replaced" in str(e.value)
+        late.close()
+        late = frb.SharedFrame(name, 4096, 2, 1)          # attaches to the new file
+        fresh.array[:4] = (1, 2, 3, 4)
+        assert list(late.array[:4]) == [1, 2, 3, 4]
+    finally:
+        late.close()
+        fresh.close()
+        crashed._h and crashed._lib.frb_shared_frame_close(crashed._h)
+    assert not os.path.exists("/dev/shm" + name) and not os.path.exists("/tmp" + name)
 
 
 def test_assemble_matches_any_world():

@@ -126,6 +126,88 @@ def test_c4_shards_vs_oracle(gpu):
         assert_parity(gpu, cfg, ref, shard=sh, what=f"C4 shard {idx}/128")
 
 
+def test_c4_whole_frame_total_and_the_eight_way_partition(gpu):
+    """All 268 Mpx of C4.  (i) The survey's independent exact total (574 496 116 940 loop-body executions) is a
+    size-independent checksum of every pixel: one whole-frame render must report it.  (ii) The partition the 8-GPU run actually
+    uses — Shard(r, 8, 16), 2048 rows each — rendered shard by shard: the shards' totals add up to the same number, each equals the
+    sum over its own counts, and on 32 sampled rows of EVERY shard (256 rows, spread over the frame) counts and final-z bits equal
+    the oracle's."""
+    torch = pytest.importorskip("torch")
+    cfg = configs.c4()
+    want_total = configs.TOTAL_ITERATIONS["C4"]
+    assert want_total == 574_496_116_940
+    n = cfg.width * cfg.height * 3
+    dev = torch.empty(n + 64, dtype=torch.uint8, device="cuda")
+    gpu.render_device_async(cfg, dev.data_ptr(), n, gpu.FRB_RGB24, device=0)
+    st = gpu.sync_stats()
+    assert st["iterations"] == want_total and st["pixels"] == cfg.width * cfg.height
+    whole_rows = dev[:n].view(cfg.height, cfg.width * 3)
+    total = 0
+    for r in range(8):
+        sh = gpu.Shard(r, 8, 16)
+        iters, z = gpu.render_counts(cfg, shard=sh)
+        s = gpu.last_stats()
+        assert iters.shape == (2048, cfg.width)
+        assert s["iterations"] == int((np.minimum(iters, cfg.iterations - 1).astype(np.uint64) + 1).sum()), f"shard {r}: total != sum of its counts"
+        total += s["iterations"]
+        local = np.arange(3 + 5 * r, 2048, 64, dtype=np.int64)            # 32 local rows, a different phase per shard
+        image_rows = sh.image_rows(cfg.height)[local].astype(np.uint32)
+        ref = ob.render_rows(cfg, rows=image_rows)
+        assert np.array_equal(iters[local], ref["iters"]), f"shard {r}/8: counts differ"
+        assert z_equal(z[local], ref["z"]).all(), f"shard {r}/8: final positions differ"
+        # and the whole-frame image holds the same rows, within the colour tolerance of the oracle
+        got = whole_rows[torch.as_tensor(image_rows.astype(np.int64), device="cuda")].cpu().numpy().reshape(len(local), cfg.width, 3)
+        assert np.abs(got.astype(int) - ref["rgb"].astype(int)).max() <= COLOUR_TOL, f"shard {r}/8: colour"
+        del iters, z
+    assert total == want_total
+
+
+def test_c5_three_whole_frames_at_true_size(gpu):
+    """Config 5, every row of the first, the middle and the last frame of the zoom (1920x1080 each) against the oracle."""
+    for k in (0, 120, 239):
+        cfg = configs.c5_frame(k)
+        ref = ob.render_rows(cfg)
+        assert_parity(gpu, cfg, ref, what=f"C5 frame {k}")
+
+
+def test_streamed_frames_under_a_co_tenant_animation(gpu):
+    """The streamed path's bounded device-side waits under real contention (src/gui.rs:60 + :325: render thread and screenshot
+    thread on one device): while frb_render_frames keeps two expensive C5 frames in flight on device 0, a second thread renders
+    a 1.8 Mpx frame into PINNED memory 60 times — the destination the streaming finisher writes while the iterate kernel runs.
+    Every image must equal the quiet render; how often the finisher had to fall back (one more launch) is printed."""
+    import time
+    anim = [configs.c5_frame(150 + (k % 40)) for k in range(140)]
+    cfg = configs.c2().with_(width=1500, height=1200)
+    n = cfg.width * cfg.height * 3
+    buf = gpu.pinned_empty(n)
+    gpu.get_image_into(cfg, buf, gpu.FRB_RGB24, device=0)
+    want = buf.copy()
+    quiet_launches = gpu.last_stats()["kernel_launches"]
+    errors = []
+
+    def animate():
+        try:
+            gpu.render_frames(anim, gpu.FRB_RGB24, device=0)
+        except Exception as e:  # noqa: BLE001 - reported below
+            errors.append(repr(e))
+
+    th = threading.Thread(target=animate)
+    th.start()
+    time.sleep(0.02)
+    done = during = fallbacks = 0
+    while done < 60:
+        buf[:] = 0x5A
+        gpu.get_image_into(cfg, buf, gpu.FRB_RGB24, device=0)
+        assert np.array_equal(buf, want), f"frame {done} rendered beside the animation differs"
+        fallbacks += gpu.last_stats()["kernel_launches"] != quiet_launches
+        done += 1
+        during += th.is_alive()
+    th.join()
+    assert not errors, errors
+    print(f"co-tenant: {during} of {done} pinned frames completed while the animation ran, {fallbacks} took the fallback path")
+    assert during >= 10, f"only {during} frames overlapped the animation"
+
+
 def test_c5_frames(gpu):
     """Three frames of the zoom through frb_render_frames (the animation entry point), against the oracle."""
     ks = [0, 100, 239]
