@@ -153,6 +153,7 @@ struct DeviceCtx {
     struct BufSet {
         cudaEvent_t ev_guard = nullptr;  // completion of the last render that used this set
         cudaStream_t last_stream = nullptr;
+        uint64_t last_use = 0;           // DeviceCtx::use_tick of that render (frb_render_device_async gives a new stream the older set)
         bool have_guard = false;
         double *tab = nullptr;           // grow-only
         size_t tab_cap = 0;              // doubles
@@ -167,6 +168,7 @@ struct DeviceCtx {
         unsigned long long *stats = nullptr;
     } sets[2];
     int cur_set = 0;
+    uint64_t use_tick = 0;
     BufSet &b() { return sets[cur_set]; }
     // Barnsley fern (frb_render_fern): per-virtual-thread hit counts and the colour table, grow-only
     uint32_t *fern_counts = nullptr;
@@ -1043,6 +1045,7 @@ int finish_enqueue(DeviceCtx &c, Slot &slot, cudaStream_t st)
     CU(cudaEventRecord(c.b().ev_guard, st));
     c.b().have_guard = true;
     c.b().last_stream = st;
+    c.b().last_use = ++c.use_tick;
     return FRB_OK;
 }
 
@@ -1971,11 +1974,16 @@ int frb_render_device_async(const FrbConfig *cfg, const FrbShard *shard, void *d
     cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
     // Renders issued on two different caller streams use the two sets of device buffers (tables, records, queue, statistics),
     // so they can overlap like the frames of frb_render_frames: the next frame's persistent CTAs start on every SM the moment
-    // the previous frame's CTA leaves it, and its shade kernel runs beside them.  A stream keeps the set it used last; a new
-    // stream takes the other one.  Same stream, or the library's own: set 0, strictly in order, as before.
+    // the previous frame's CTA leaves it, and its shade kernel runs beside them.  A stream keeps the set it used last; a stream
+    // that owns neither takes the set that has been idle longer — so two caller streams end up on different sets whatever ran
+    // before them (a blocking render in between leaves set 0 with the library's stream: "the other one" then put BOTH caller
+    // streams on set 1, one frame at a time).  The library's own stream: set 0, strictly in order, as before.
     int set = 0;
-    if (c->sets[1].have_guard && c->sets[1].last_stream == st) set = 1;
-    else if (c->sets[0].have_guard && c->sets[0].last_stream != st && stream != nullptr) set = 1;
+    if (stream != nullptr) {
+        if (c->sets[1].have_guard && c->sets[1].last_stream == st) set = 1;
+        else if (c->sets[0].have_guard && c->sets[0].last_stream == st) set = 0;
+        else if (c->sets[0].have_guard && (!c->sets[1].have_guard || c->sets[1].last_use < c->sets[0].last_use)) set = 1;
+    }
     struct SetGuard {
         DeviceCtx *c;
         ~SetGuard() { c->cur_set = 0; }

@@ -275,3 +275,41 @@ def test_device_async_on_two_streams_overlaps_and_stays_exact(gpu):
     for j, cfg in enumerate(scenes):   # statistics of the last frames are still readable, and a single stream still works
         got, st = render_device(gpu, cfg, 3)
         assert np.array_equal(got, refs[j])
+
+
+def test_two_caller_streams_overlap_even_after_a_blocking_render(gpu):
+    """A blocking render leaves buffer set 0 with the library's own stream.  Two caller streams that come next must still end up
+    on DIFFERENT sets (round 3: both used to land on set 1 and ran one frame at a time — bench.py's per-workload device arm after
+    an end-to-end arm).  Overlap is observable as throughput: two streams must beat one stream on the same frames."""
+    cfg = configs.c1()                       # a short frame: its tail and launch gaps are a third of it, so overlap shows
+    n = cfg.width * cfg.height * 3
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    outs = [torch.empty(n + 64, dtype=torch.uint8, device="cuda") for _ in streams]
+    ref = gpu.get_image(cfg).reshape(-1)     # the blocking render (also the reference bytes)
+
+    def timed(use, frames=400):
+        for k in range(8):
+            gpu.render_device_async(cfg, outs[k % use].data_ptr(), n, 3, device=0, stream=streams[k % use].cuda_stream)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(streams[0])
+        for st in streams[1:use]:
+            st.wait_event(e0)
+        for k in range(frames):
+            gpu.render_device_async(cfg, outs[k % use].data_ptr(), n, 3, device=0, stream=streams[k % use].cuda_stream)
+        for st in streams[1:use]:
+            done = torch.cuda.Event()
+            done.record(st)
+            streams[0].wait_event(done)
+        e1.record(streams[0])
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / frames
+
+    two = timed(2)
+    gpu.get_image(cfg)                       # set 0 goes back to the library's stream
+    two_after = timed(2)
+    one = timed(1)
+    for o in outs:
+        assert np.array_equal(o[:n].cpu().numpy(), ref)
+    assert two_after < 0.9 * one, f"two streams {two_after:.4f} ms/frame vs one stream {one:.4f}: no overlap after a blocking render"
+    assert two_after < 1.15 * two, f"two streams after a blocking render {two_after:.4f} ms/frame vs before {two:.4f}"
