@@ -804,7 +804,8 @@ def main():
                           "step_frac is over the headline arm (two frames in flight)",
         "peak_source": "measured in this run: frb_measure_fp64_peak DFMA stream x 2 flop (MEASURED_PEAKS.json has no FP64 entry; the same "
                        "measurement with its clock sample is kept in profiles/r3_fp64_peak.json)",
-        "peak_sm_clock_mhz": round(peak.get("sm_clock_mhz", 0.0), 1),
+        # one DFMA per FP64 lane per cycle: the rate itself says what clock the pipe ran at (nvidia-smi's sample is in `clocks`)
+        "peak_implied_sm_clock_mhz": round(peak["dfma_per_s"] / (peak["sm_count"] * 64) / 1e6, 1),
         "peak_nominal": FP64_NOMINAL_TFLOPS, "frac_of_nominal": round(achieved_tflops / FP64_NOMINAL_TFLOPS, 4),
         "fp64_instr_per_iter": form,
         "pipe_frac": round(per_launch_iters * form / (it_ms * 1e-3) / peak["dfma_per_s"], 4),

@@ -135,7 +135,11 @@ extern "C" int frb_measure_fp64_peak(int device, FrbFp64Peak *peak)
     if (e == cudaSuccess) e = run_one<OP_MIX6>(blocks, trips, sink, cycles, &peak->mixed6_per_s, &mhz[3]);
     cudaFree(sink);
     cudaFree(cycles);
-    peak->sm_clock_mhz = mhz[0];
+    // One DFMA per FP64 lane per cycle, 64 lanes per SM: the measured rate itself says what clock the pipe ran at.  (The
+    // clock64 bracket of block 0 over the event time, mhz[], read 491 MHz on a B200 whose nvidia-smi samples said 1965 all along
+    // — a quarter, for a reason not yet tracked down — so it is no longer what is reported.)
+    (void)mhz;
+    peak->sm_clock_mhz = peak->dfma_per_s / ((double)prop.multiProcessorCount * 64.0) / 1e6;
     peak->sm_count = (uint32_t)prop.multiProcessorCount;
     peak->reserved = 0;
     return e == cudaSuccess ? FRB_OK : FRB_ERR_CUDA;

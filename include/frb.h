@@ -377,7 +377,7 @@ typedef struct FrbFp64Peak {
     double dmul_per_s;
     double dadd_per_s;
     double mixed6_per_s;  /* the 6-instruction iteration body as an independent stream (no exits) */
-    double sm_clock_mhz;  /* average SM clock observed during the run (clock64 / event time) */
+    double sm_clock_mhz;  /* SM clock implied by the DFMA rate: dfma_per_s / (sm_count x 64 FP64 lanes) */
     uint32_t sm_count;
     uint32_t reserved;
 } FrbFp64Peak;

@@ -7,7 +7,7 @@ python bench.py --impl reference > gpurun_out/${tag}_bench_C2_reference_arm.json
 for w in C1 C2 C3 C4; do python - <<PY
 import json
 d=json.loads(open("gpurun_out/${tag}_bench_${w}_n1.json").read()); r=d["roofline"]
-print("$w", d["config"]["kernel"], "kernel_ms", r["kernel_ms"], "shade", r["shade_kernel_ms"], "frac", r["frac"], "frame", d["ms_per_frame"], d["value"], "e2e", d["e2e"]["ms_per_frame"], d["e2e"]["value"], "pinned", d["e2e_pinned"]["ms_per_frame"], "launches", d["gpu_launches"], "clocks", d["clocks"]["sm_mhz"], d["clocks"]["reasons"])
+print("$w", d["run"]["kernel"], "kernel_ms", r["kernel_ms"], "shade", r["shade_kernel_ms"], "frac", r["frac"], "frame", d["ms_per_frame"], d["value"], "e2e", d["e2e"]["ms_per_frame"], d["e2e"]["value"], "pinned", d["e2e_pinned"]["ms_per_frame"], "launches", d["gpu_launches"], "clocks", d["clocks"]["sm_mhz"], d["clocks"]["reasons"])
 PY
 done
 python -c "
